@@ -1,0 +1,166 @@
+// common.cuh -- shared device/host helpers for the gd_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <atomic>
+
+#include "../../include/gd_b200.h"
+
+namespace gd {
+
+// ------------------------------------------------------------------ host-side error plumbing
+void set_error(const char* fmt, ...);
+extern std::atomic<long long> g_launches;
+
+#define GD_REQUIRE(cond, ...)                                 \
+  do {                                                        \
+    if (!(cond)) {                                            \
+      gd::set_error(__VA_ARGS__);                             \
+      return GD_ERR_INVALID;                                  \
+    }                                                         \
+  } while (0)
+
+#define GD_CUDA_OK(expr)                                                              \
+  do {                                                                                \
+    cudaError_t e__ = (expr);                                                         \
+    if (e__ != cudaSuccess) {                                                         \
+      gd::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return GD_ERR_CUDA;                                                             \
+    }                                                                                 \
+  } while (0)
+
+#define GD_LAUNCH_CHECK()                                                             \
+  do {                                                                                \
+    gd::g_launches.fetch_add(1, std::memory_order_relaxed);                           \
+    cudaError_t e__ = cudaGetLastError();                                             \
+    if (e__ != cudaSuccess) {                                                         \
+      gd::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return GD_ERR_CUDA;                                                             \
+    }                                                                                 \
+  } while (0)
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// ------------------------------------------------------------------ device helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+
+// ------------------------------------------------------------------ fused GEMM epilogue
+// Processes CH consecutive columns [n0, n0+CH) of logical row m.  See gdEpilogue in gd_b200.h.
+template <int CH>
+__device__ __forceinline__ void epilogue_row_chunk(const gdEpilogue& ep, int m, int n0, int N,
+                                                   float (&v)[CH]) {
+  const int nvalid = min(CH, N - n0);
+  if (nvalid <= 0) return;
+  if (ep.bias) {
+#pragma unroll
+    for (int i = 0; i < CH; ++i)
+      if (i < nvalid) v[i] += __ldg(ep.bias + n0 + i);
+  }
+  if (ep.rowtab) {
+    const float* tr = ep.rowtab + (size_t)((m % ep.tab_period) + ep.tab_offset) * ep.ld_tab + n0;
+#pragma unroll
+    for (int i = 0; i < CH; ++i)
+      if (i < nvalid) v[i] += __ldg(tr + i);
+  }
+  const int ncopy = ep.dup > 1 ? ep.dup : 1;
+  int base_row = m;
+  if (ep.map_t > 0) base_row = (m / ep.map_t) * ep.map_s + ep.map_off + (m % ep.map_t);
+  for (int c = 0; c < ncopy; ++c) {
+    float w[CH];
+#pragma unroll
+    for (int i = 0; i < CH; ++i) w[i] = v[i];
+    if (ep.seqbias) {
+      const float* sb = ep.seqbias + (size_t)(c * ep.seq_count + m / ep.seq_rows) * ep.ld_seq + n0;
+#pragma unroll
+      for (int i = 0; i < CH; ++i)
+        if (i < nvalid) w[i] += __ldg(sb + i);
+    }
+    const size_t r = (size_t)base_row + (size_t)c * ep.dup_row_stride;
+    if (ep.residual) {
+      const float* rr = ep.residual + r * ep.ld_res + n0;
+      if (nvalid == CH && (CH % 4 == 0) && ((((size_t)rr) & 15) == 0)) {
+#pragma unroll
+        for (int i = 0; i < CH; i += 4) {
+          float4 q = *reinterpret_cast<const float4*>(rr + i);
+          w[i] += q.x; w[i + 1] += q.y; w[i + 2] += q.z; w[i + 3] += q.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (i < nvalid) w[i] += rr[i];
+      }
+    }
+    if (ep.act == GD_ACT_GELU_ERF) {
+#pragma unroll
+      for (int i = 0; i < CH; ++i) w[i] = gelu_erf(w[i]);
+    } else if (ep.act == GD_ACT_SILU) {
+#pragma unroll
+      for (int i = 0; i < CH; ++i) w[i] = silu(w[i]);
+    }
+    if (ep.out_t) {
+      const int seq = m / ep.t_s, s = m % ep.t_s;
+      if (s >= ep.t_skip) {
+        float* o = ep.out_t + ((size_t)seq * N + n0) * ep.t_t + (s - ep.t_skip);
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (i < nvalid) o[(size_t)i * ep.t_t] = w[i];
+      }
+      continue;
+    }
+    if (ep.out_f32) {
+      float* o = ep.out_f32 + r * ep.ld_out + n0;
+      if (nvalid == CH && (CH % 4 == 0) && ((((size_t)o) & 15) == 0)) {
+#pragma unroll
+        for (int i = 0; i < CH; i += 4)
+          *reinterpret_cast<float4*>(o + i) = make_float4(w[i], w[i + 1], w[i + 2], w[i + 3]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (i < nvalid) o[i] = w[i];
+      }
+    }
+    if (ep.out_bf16) {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out_bf16) + r * ep.ld_out_bf16 + n0;
+      if (nvalid == CH && (CH % 8 == 0) && ((((size_t)o) & 15) == 0)) {
+#pragma unroll
+        for (int i = 0; i < CH; i += 8) {
+          uint4 q;
+          q.x = pack_bf16x2(w[i], w[i + 1]);
+          q.y = pack_bf16x2(w[i + 2], w[i + 3]);
+          q.z = pack_bf16x2(w[i + 4], w[i + 5]);
+          q.w = pack_bf16x2(w[i + 6], w[i + 7]);
+          *reinterpret_cast<uint4*>(o + i) = q;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (i < nvalid) o[i] = __float2bfloat16_rn(w[i]);
+      }
+    }
+  }
+}
+
+int validate_epilogue(const gdEpilogue* ep, int M, int N);
+
+}  // namespace gd

@@ -1,0 +1,241 @@
+// gemm_tcgen05.cu -- persistent warp-specialised bf16 GEMM for sm_100a.
+//   C[M,N] = A[M,K] @ W[N,K]^T  (+ fused gdEpilogue), fp32 accumulation in TMEM.
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = UMMA issuer (one elected lane),
+// warps 2..9 = epilogue (TMEM -> registers -> fused epilogue -> global).  The accumulator is
+// double buffered in TMEM (2 x BN fp32 columns) so the epilogue of tile i overlaps the MMAs of
+// tile i+1; A/W tiles stream through a kStages-deep TMA/mbarrier ring with 128B swizzle.
+// Replaces every aten::addmm of the reference hot path (see gd_b200.h).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace gd {
+
+constexpr int kBM = 128;          // UMMA M (cta_group::1)
+constexpr int kBK = 64;           // 64 bf16 = 128 B = one swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kEpiWarps = 8;
+constexpr int kGemmThreads = (2 + kEpiWarps) * 32;
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kABytes = kBM * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;   // +1024 alignment slack
+  static constexpr int kTmemCols = 2 * BN;                                      // 256 or 512 (power of 2)
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                         int M, int N, int K, const gdEpilogue ep) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* bars = smem + Cfg::kStages * Cfg::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bars);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m_tiles = (M + kBM - 1) / kBM;
+  const int n_tiles = (N + BN - 1) / BN;
+  const int total_tiles = m_tiles * n_tiles;
+  const int k_blocks = (K + kBK - 1) / kBK;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_a);
+    ptx::prefetch_tensormap(&tmap_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(&tfull_bar[b], 1);
+      ptx::mbar_init(&tempty_bar[b], kEpiWarps);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
+          ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kBK, n_blk * BN);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ UMMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16_f32(kBM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+        const int buf = local & 1;
+        const uint32_t use = (uint32_t)(local >> 1);
+        ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);     // epilogue drained this accumulator
+        ptx::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            const uint64_t da = ptx::umma_desc_k_sw128(sa + k * kUmmaK * 2);
+            const uint64_t db = ptx::umma_desc_k_sw128(sb + k * kUmmaK * 2);
+            ptx::umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);               // smem slot reusable when MMAs retire
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        ptx::umma_commit(&tfull_bar[buf]);                   // accumulator complete
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps
+    const int ew = warp - 2;
+    const int quarter = warp & 3;            // TMEM lane quarter this warp may access
+    const int half = ew >> 2;                // which half of the BN columns
+    constexpr int kColsPerWarp = BN / 2;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int buf = local & 1;
+      const uint32_t use = (uint32_t)(local >> 1);
+      ptx::mbar_wait(&tfull_bar[buf], use & 1);
+      ptx::tc_fence_after();
+      const int m = m_blk * kBM + quarter * 32 + lane;
+      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
+#pragma unroll 1
+      for (int c = 0; c < kColsPerWarp; c += 32) {
+        float v[32];
+        ptx::tmem_ld_32x32(taddr0 + c, v);
+        const int n0 = n_blk * BN + half * kColsPerWarp + c;
+        if (m < M && n0 < N) epilogue_row_chunk<32>(ep, m, n0, N, v);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty_bar[buf]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess || p == nullptr) {
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// 2D bf16 row-major [rows, cols] with row stride ld elements; box = [box_rows, 64 cols], SW128.
+static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    return GD_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%d cols=%d ld=%d)", (int)r, rows, cols, ld);
+    return GD_ERR_CUDA;
+  }
+  return GD_OK;
+}
+
+static int g_num_sms = 0;
+
+template <int BN>
+static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const gdEpilogue* ep,
+                       cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  CUtensorMap ta, tw;
+  int rc = make_tmap(&ta, A, M, K, lda, kBM);
+  if (rc) return rc;
+  rc = make_tmap(&tw, W, N, K, ldw, BN);
+  if (rc) return rc;
+  const int tiles = ceil_div(M, kBM) * ceil_div(N, BN);
+  const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+  gemm_bf16_tcgen05_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tw, M, N, K, *ep);
+  GD_LAUNCH_CHECK();
+  return GD_OK;
+}
+
+}  // namespace gd
+
+extern "C" int gd_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                            const gdEpilogue* ep, void* stream) {
+  using namespace gd;
+  GD_REQUIRE(A && W && ep, "gd_gemm_bf16: null pointer");
+  GD_REQUIRE(M > 0 && N > 0 && K > 0, "gd_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
+  GD_REQUIRE(lda % 8 == 0 && ldw % 8 == 0 && lda >= K && ldw >= K,
+             "gd_gemm_bf16: lda/ldw must be multiples of 8 and >= K (lda=%d ldw=%d K=%d)", lda, ldw, K);
+  GD_REQUIRE((((uintptr_t)A) & 15) == 0 && (((uintptr_t)W) & 15) == 0, "gd_gemm_bf16: operands must be 16B aligned");
+  int rc = validate_epilogue(ep, M, N);
+  if (rc) return rc;
+  if (g_num_sms == 0) {
+    int dev = 0;
+    GD_CUDA_OK(cudaGetDevice(&dev));
+    GD_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  // Tile choice: BN=256 halves A re-reads and epilogue barrier traffic; BN=128 gives finer waves.
+  const long tiles256 = (long)ceil_div(M, kBM) * ceil_div(N, 256);
+  const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms);
+  if (use256) return launch_gemm<256>(A, lda, W, ldw, M, N, K, ep, (cudaStream_t)stream);
+  return launch_gemm<128>(A, lda, W, ldw, M, N, K, ep, (cudaStream_t)stream);
+}

@@ -1,0 +1,154 @@
+// local_attention.cu -- RoPE -> causal windowed LocalAttention -> RoPE of the V2 denoiser
+// (mdm.py:176-213; local_attention.py:43-62 SinusoidalEmbeddings/rotate_half/apply_rotary_pos_emb,
+//  :92-172 LocalAttention.forward with window 10, look_backward 1, look_forward 0, q = k = v),
+// and the per-step conditioning token (mdm.py:130,154-160,197; mdm_old.py:94-99,109-112).
+//
+// One CTA per (sequence, head): the [T, e] head slab is read once from HBM (fp32), rotated with the
+// cos/sin tables and kept in shared memory (row stride e+1 -> conflict-free row-parallel reads);
+// each warp then owns query rows: lanes = keys (<= 2*window) for the scores, shuffle softmax,
+// lanes = channels for the PV sum, second rotation at position t+1, coalesced fp32 + bf16 stores
+// straight into rows 1..T of the encoder input.  HBM-bound: 4 B/elem in, 4 (+2) B/elem out.
+// Semantics kept from the reference: the query at in-window offset i of window w attends to all of
+// window w-1 and to offsets 0..i of window w; window 0 has no look-back (its padding keys are masked,
+// contributing exactly 0); scale = e^-0.5; V is the rotated tensor as well.
+#include "common.cuh"
+
+namespace gd {
+
+constexpr int LA_THREADS = 256;
+
+__global__ void __launch_bounds__(LA_THREADS)
+local_attention_kernel(const float* __restrict__ z, const float* __restrict__ rcos, const float* __restrict__ rsin,
+                       float* __restrict__ x_f32, __nv_bfloat16* __restrict__ x_bf16, int T, int d, int e,
+                       int window, float scale) {
+  extern __shared__ float sm[];
+  const int es = e + 1;
+  float* slab = sm;                                   // [T][e+1] rotated q=k=v
+  float* scratch = sm + (size_t)T * es;               // [warps][e]
+  const int head = blockIdx.x, seq = blockIdx.y;
+  const int half = e >> 1;
+  const float* zs = z + (size_t)seq * T * d + head * e;
+  for (int idx = threadIdx.x; idx < T * e; idx += LA_THREADS) {
+    const int t = idx / e, i = idx - t * e;
+    const float x = zs[(size_t)t * d + i];
+    const float p = (i < half) ? -zs[(size_t)t * d + i + half] : zs[(size_t)t * d + i - half];
+    slab[t * es + i] = x * rcos[t * e + i] + p * rsin[t * e + i];
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* my = scratch + warp * e;
+  const int S = T + 1;
+  for (int t = warp; t < T; t += LA_THREADS / 32) {
+    const int w = t / window;
+    const int kbeg = (w > 0 ? (w - 1) * window : 0);
+    const int nk = t - kbeg + 1;                       // <= 2*window
+    const float* q = slab + t * es;
+    float out_acc[4] = {0.f, 0.f, 0.f, 0.f};           // channels lane, lane+32, ... (e <= 128)
+    float run_max = -INFINITY, run_sum = 0.f;
+    for (int kb = 0; kb < nk; kb += 32) {              // normally a single pass (nk <= 20)
+      const int k = kbeg + kb + lane;
+      float sc = -INFINITY;
+      if (kb + lane < nk) {
+        const float* kr = slab + k * es;
+        float acc = 0.f;
+        for (int i = 0; i < e; ++i) acc = fmaf(q[i], kr[i], acc);
+        sc = acc * scale;
+      }
+      const float bm = warp_max(sc);
+      const float nm = fmaxf(run_max, bm);
+      const float corr = expf(run_max - nm);           // 0 on the first pass
+      const float p = (kb + lane < nk) ? expf(sc - nm) : 0.f;
+      run_sum = run_sum * corr + warp_sum(p);
+      run_max = nm;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) out_acc[c] *= corr;
+      const int cnt = min(32, nk - kb);
+      for (int j = 0; j < cnt; ++j) {
+        const float pj = __shfl_sync(0xffffffffu, p, j);
+        const float* vr = slab + (kbeg + kb + j) * es;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int ch = lane + 32 * c;
+          if (ch < e) out_acc[c] = fmaf(pj, vr[ch], out_acc[c]);
+        }
+      }
+    }
+    const float inv = 1.0f / run_sum;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int ch = lane + 32 * c;
+      if (ch < e) my[ch] = out_acc[c] * inv;
+    }
+    __syncwarp();
+    // second rotation at sequence position t+1 (token 0 is the conditioning token)
+    const size_t orow = ((size_t)seq * S + 1 + t) * d + head * e;
+    const float* c2 = rcos + (size_t)(t + 1) * e;
+    const float* s2 = rsin + (size_t)(t + 1) * e;
+    for (int ch = lane; ch < e; ch += 32) {
+      const float x = my[ch];
+      const float p = (ch < half) ? -my[ch + half] : my[ch - half];
+      const float y = x * c2[ch] + p * s2[ch];
+      if (x_f32) x_f32[orow + ch] = y;
+      if (x_bf16) x_bf16[orow + ch] = __float2bfloat16_rn(y);
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(128)
+cond_tokens_kernel(const long long* __restrict__ t, const float* __restrict__ temb, const float* __restrict__ seed_emb,
+                   const float* __restrict__ pe0, const float* __restrict__ coarse_tab,
+                   const float* __restrict__ coarse_seed, float* __restrict__ coarse_out, float* __restrict__ x_f32,
+                   __nv_bfloat16* __restrict__ x_bf16, int B, int S, int d) {
+  const int b = blockIdx.x, c = blockIdx.y;
+  const long long tt = t[b];
+  const size_t srow = (size_t)(c * B + b);
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    float v = temb[(size_t)tt * d + i] + seed_emb[srow * d + i];
+    if (pe0) v += pe0[i];
+    if (x_f32) x_f32[srow * S * d + i] = v;
+    if (x_bf16) x_bf16[srow * S * d + i] = __float2bfloat16_rn(v);
+    if (coarse_out) coarse_out[srow * d + i] = coarse_tab[(size_t)tt * d + i] + coarse_seed[srow * d + i];
+  }
+}
+
+}  // namespace gd
+
+extern "C" int gd_local_attention(const float* z, const float* rope_cos, const float* rope_sin, float* x_f32,
+                                  void* x_bf16, int32_t n_seq, int32_t T, int32_t d, int32_t heads, int32_t window,
+                                  void* stream) {
+  using namespace gd;
+  GD_REQUIRE(z && rope_cos && rope_sin && (x_f32 || x_bf16), "gd_local_attention: null pointer");
+  GD_REQUIRE(n_seq > 0 && n_seq <= 65535 && T > 0 && heads > 0 && d % heads == 0, "gd_local_attention: bad shape");
+  GD_REQUIRE(window > 0 && T % window == 0,
+             "sequence length must be divisible by window size for local attention (T=%d, window=%d)", T, window);
+  const int e = d / heads;
+  GD_REQUIRE(e % 2 == 0 && e <= 128, "gd_local_attention: head dim %d must be even and <= 128", e);
+  const size_t smem = ((size_t)T * (e + 1) + (LA_THREADS / 32) * e) * sizeof(float);
+  GD_REQUIRE(smem <= 200 * 1024, "gd_local_attention: T=%d too long for the shared-memory slab", T);
+  static size_t set = 0;
+  if (smem > 48 * 1024 && smem > set) {
+    GD_CUDA_OK(cudaFuncSetAttribute(local_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    set = smem;
+  }
+  dim3 grid(heads, n_seq);
+  local_attention_kernel<<<grid, LA_THREADS, smem, (cudaStream_t)stream>>>(
+      z, rope_cos, rope_sin, x_f32, (__nv_bfloat16*)x_bf16, T, d, e, window, 1.0f / sqrtf((float)e));
+  GD_LAUNCH_CHECK();
+  return GD_OK;
+}
+
+extern "C" int gd_cond_tokens(const int64_t* t, const float* temb_table, const float* seed_emb, const float* pe0,
+                              const float* coarse_tab, const float* coarse_seed, float* coarse_out, float* x_f32,
+                              void* x_bf16, int32_t B, int32_t n_branch, int32_t S, int32_t d, void* stream) {
+  using namespace gd;
+  GD_REQUIRE(t && temb_table && seed_emb && (x_f32 || x_bf16 || coarse_out), "gd_cond_tokens: null pointer");
+  GD_REQUIRE(B > 0 && n_branch > 0 && n_branch <= 65535 && S > 0 && d > 0, "gd_cond_tokens: bad shape");
+  GD_REQUIRE(!coarse_out || (coarse_tab && coarse_seed), "gd_cond_tokens: coarse_out needs coarse_tab and coarse_seed");
+  dim3 grid(B, n_branch);
+  cond_tokens_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>((const long long*)t, temb_table, seed_emb, pe0, coarse_tab,
+                                                            coarse_seed, coarse_out, x_f32, (__nv_bfloat16*)x_bf16, B,
+                                                            S, d);
+  GD_LAUNCH_CHECK();
+  return GD_OK;
+}

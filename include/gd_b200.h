@@ -1,0 +1,170 @@
+/* gd_b200.h -- C ABI of the B200-native GestureDiffusion/MDM sampling hot path.
+ *
+ * The reference (AI-Unicamp/GestureDiffusion) has no native code and no FFI: its
+ * "plugin API" is the Python surface of diffusion/respace.py, diffusion/gaussian_diffusion.py,
+ * model/mdm.py, model/mdm_old.py and model/cfg_sampler.py.  This header is the boundary
+ * that a Python (ctypes) binding of that surface calls; every entry point names the
+ * reference code it replaces (file:line, relative to the reference root).
+ *
+ * Conventions
+ *  - plain pointers and sizes only; all pointers are DEVICE pointers unless noted;
+ *  - `stream` is a cudaStream_t passed as void*; nothing synchronises, allocates or reads
+ *    back inside a call, so every call is CUDA-graph capturable;
+ *  - return 0 on success, negative gdStatus otherwise; gd_last_error() gives the message
+ *    (thread-local, host pointer);
+ *  - row-major everywhere; "act" buffers are bf16 in bf16 mode and fp32 in fp32 mode;
+ *  - weights use the nn.Linear layout W[N][K] (K contiguous) exactly as in the reference
+ *    state_dict, so y = x @ W^T + b.
+ */
+#ifndef GD_B200_H
+#define GD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GD_ABI_VERSION 1
+
+typedef enum gdStatus {
+  GD_OK = 0,
+  GD_ERR_INVALID = -1,   /* bad argument (shape, alignment, null pointer) */
+  GD_ERR_CUDA = -2,      /* a CUDA runtime/driver call failed */
+  GD_ERR_UNSUPPORTED = -3
+} gdStatus;
+
+typedef enum gdAct { GD_ACT_NONE = 0, GD_ACT_GELU_ERF = 1, GD_ACT_SILU = 2 } gdAct;
+
+/* Fused GEMM epilogue.  For accumulator element (m, n) of  A[M,K] @ W[N,K]^T :
+ *   v  = acc + bias[n] + rowtab[((m % tab_period) + tab_offset) * ld_tab + n]
+ *   for copy c in [0, dup):                      (dup = 0 or 1 means a single copy)
+ *     w = v + seqbias[(c * seq_count + m / seq_rows) * ld_seq + n]
+ *     r = rowmap(m) + c * dup_row_stride         rowmap(m) = (m / map_t) * map_s + map_off + m % map_t
+ *                                                 (identity when map_t == 0)
+ *     w += residual[r * ld_res + n];  w = act(w)
+ *     out_f32[r * ld_out + n] = w;  out_bf16[r * ld_out_bf16 + n] = bf16(w)
+ *   transposed store (out_t != NULL, replaces the row-major stores):
+ *     seq = m / t_s, s = m % t_s;  if (s >= t_skip) out_t[((seq * N + n) * t_t) + s - t_skip] = w
+ * Every pointer may be NULL to disable that term.  This covers, with one GEMM each:
+ *   InputProcess + additive PositionalEncoding (mdm_old.py:102-112), project_to_lat with its
+ *   per-sample coarse term (mdm.py:151-169), in_proj/out_proj/linear1/linear2 with bias, erf-GELU
+ *   and the residual add of nn.TransformerEncoderLayer (mdm.py:90-96), and OutputProcess with
+ *   its [T,B,J]->[B,J,1,T] permute and the output[1:] slice (mdm.py:219-222, 372-380). */
+typedef struct gdEpilogue {
+  const float* bias;
+  const float* rowtab;   int32_t tab_period, tab_offset, ld_tab;
+  const float* seqbias;  int32_t seq_rows, seq_count, ld_seq;
+  const float* residual; int32_t ld_res;
+  int32_t act;
+  int32_t map_t, map_s, map_off;
+  int32_t dup, dup_row_stride;
+  float* out_f32;        int32_t ld_out;
+  void*  out_bf16;       int32_t ld_out_bf16;
+  float* out_t;          int32_t t_s, t_t, t_skip;
+} gdEpilogue;
+
+int gd_abi_version(void);
+const char* gd_last_error(void);                 /* host string, thread-local */
+
+/* Dense projections (replace every aten::addmm on the path: mdm.py:350-356, 151-169, 90-96,
+ * 372-380; mdm_old.py:102-118).  bf16: tcgen05.mma (UMMA 128xBNx16, fp32 accumulate in TMEM),
+ * operands staged by TMA with 128B swizzle; requires sm_100a, lda/ldw multiples of 8 elements and
+ * 16-byte aligned bases.  f32: SIMT fp32 reference-precision path ("fp32 mode" + one-off setup). */
+int gd_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw,
+                 int32_t M, int32_t N, int32_t K, const gdEpilogue* ep, void* stream);
+int gd_gemm_f32(const float* A, int32_t lda, const float* W, int32_t ldw,
+                int32_t M, int32_t N, int32_t K, const gdEpilogue* ep, void* stream);
+
+/* Full softmax self-attention of nn.MultiheadAttention inside nn.TransformerEncoderLayer
+ * (mdm.py:90-96,216; no mask, scale 1/sqrt(head_dim)).  qkv is the packed in_proj output
+ * [n_seq*S, 3*d] (q | k | v, heads contiguous inside each); out is [n_seq*S, d]. */
+int gd_attention_bf16(const void* qkv, void* out, int32_t n_seq, int32_t S, int32_t n_heads,
+                      int32_t head_dim, void* stream);
+int gd_attention_f32(const float* qkv, float* out, int32_t n_seq, int32_t S, int32_t n_heads,
+                     int32_t head_dim, void* stream);
+
+/* LayerNorm (norm1/norm2 of nn.TransformerEncoderLayer, eps 1e-5): rows x d fp32 in,
+ * fp32 and/or bf16 out (either may be NULL). */
+int gd_layernorm(const float* in, const float* gamma, const float* beta, float* out_f32,
+                 void* out_bf16, int32_t rows, int32_t d, float eps, void* stream);
+
+/* RoPE + causal windowed LocalAttention + second RoPE (mdm.py:176-213; local_attention.py:43-62,
+ * 92-172): z [n_seq, T, d] fp32 -> encoder-input rows 1..T of each sequence (token 0 is written by
+ * gd_cond_tokens): x_f32 / x_bf16 [n_seq, T+1, d].  q = k = v, `heads` heads of e = d/heads, window
+ * `window`, one window of look-back; rope_cos/rope_sin are fp32 [T+1, e] tables of
+ * cos/sin(cat(pos x inv_freq, pos x inv_freq)) built from the checkpoint's rel_pos.inv_freq: rows 0..T-1
+ * rotate the attention input, rows 1..T rotate its output (the cond token sits at position 0).
+ * T must be a multiple of `window` (the reference fails otherwise, local_attention.py:100-112). */
+int gd_local_attention(const float* z, const float* rope_cos, const float* rope_sin, float* x_f32,
+                       void* x_bf16, int32_t n_seq, int32_t T, int32_t d, int32_t heads, int32_t window,
+                       void* stream);
+
+/* Per-step conditioning token (mdm_old.py:94-99,109-112; mdm.py:130,154-160,197):
+ *   tok[c, b, :] = temb_table[t[b], :] + seed_emb[c, b, :] (+ pe0[:])      c in [0, n_branch)
+ * written to row (c*B + b) * S of x_f32 / x_bf16 (row stride d), and optionally
+ *   coarse_out[c*B + b, :] = coarse_tab[t[b], :] + coarse_seed[c, b, :]
+ * (the W_c . coa term of project_to_lat, by linearity).  t is int64 [B] of ORIGINAL-schedule
+ * timesteps (respace.py:124-129 already applied). */
+int gd_cond_tokens(const int64_t* t, const float* temb_table, const float* seed_emb, const float* pe0,
+                   const float* coarse_tab, const float* coarse_seed, float* coarse_out,
+                   float* x_f32, void* x_bf16, int32_t B, int32_t n_branch, int32_t S, int32_t d,
+                   void* stream);
+
+/* The fused guidance + posterior + noise update (cfg_sampler.py:28; gaussian_diffusion.py:253-275,
+ * 307-311, 354-376, 532-547).  All motion tensors are [B, J, T] fp32 (== [B,J,1,T]).
+ *   x0   = uncond ? uncond + scale[b]*(cond - uncond) : cond          (model_mean_type START_X)
+ *          (EPSILON: x0 = c_recip*x_t - c_recipm1*eps, on the guided eps)
+ *   x0   = inpaint_mask ? inpaint_mask ? inpainted : x0 ...            (optional blend)
+ *   x0   = clip ? clamp(x0,-1,1) : x0
+ *   mean = coef1*x0 + coef2*x_t ;  x_prev = mean + (step != 0) * exp(0.5*logvar) * noise
+ * Coefficients are read on the device from coef[6][n_steps] fp32 (coef1, coef2, logvar,
+ * sqrt_recip_acp, sqrt_recipm1_acp, reserved) at index *step_ptr -- the float64 tables of
+ * gaussian_diffusion.py:160-197 cast once to fp32 exactly like _extract_into_tensor (:1605).
+ * Noise: `noise` != NULL reads injected noise (const_noise -> sample 0's noise for all b), else
+ * Philox4x32-10 keyed (seed, sample_base + b (or 0 if const_noise), *step_ptr, element) is
+ * generated in-kernel.  Optional outputs: pred_xstart, mean, and the next step's GEMM operand
+ * a_next[(b*T + t) * ld_a + j] (bf16 or fp32), i.e. InputProcess's permute (mdm.py:350-352) fused
+ * into this kernel's store.  If next_t != NULL the kernel also advances the loop state on the
+ * device: step_ptr[0] -= 1 and next_t[b] = timestep_map[step-1] (respace.py:124-129). */
+typedef struct gdPosteriorArgs {
+  const float* cond; const float* uncond; const float* scale;
+  const float* x_t; const float* noise;
+  const uint8_t* inpaint_mask; const float* inpainted;
+  const float* coef; int32_t n_steps; int32_t* step_ptr;
+  const int64_t* timestep_map; int64_t* next_t;
+  float* x_prev; float* pred_xstart; float* mean;
+  void* a_next; int32_t ld_a; int32_t a_is_bf16;
+  int32_t B, J, T;
+  int32_t eps_mode, clip, const_noise;
+  uint64_t seed; int64_t sample_base;
+} gdPosteriorArgs;
+int gd_posterior_step(const gdPosteriorArgs* args, void* stream);
+
+/* InputProcess's permute for the first step / standalone forward (mdm.py:350-352, mdm_old.py:102-103):
+ * src [B, C, T] fp32 -> dst[(b*T + t) * ld + col_off + c] (bf16 or fp32). */
+int gd_pack_rows(const float* src, void* dst, int32_t B, int32_t C, int32_t T, int32_t ld,
+                 int32_t col_off, int32_t dst_is_bf16, void* stream);
+
+/* q_sample (gaussian_diffusion.py:233-251) for skip_timesteps/init_image:
+ * out = a[step]*x0 + b[step]*noise with a/b fp32 device tables. */
+int gd_q_sample(const float* x0, const float* noise, const float* sqrt_acp, const float* sqrt_1macp,
+                int32_t step, float* out, int64_t n, void* stream);
+
+/* Standalone Philox4x32-10 + Box-Muller N(0,1) fill with the same keying as gd_posterior_step
+ * (element index = (b*J + j)*T + t). */
+int gd_philox_normal(float* out, int32_t B, int32_t J, int32_t T, uint64_t seed, int64_t sample_base,
+                     int32_t step, void* stream);
+
+/* Small device helpers used by the host loop (no torch ops on the hot path). */
+int gd_set_loop_state(int32_t* step_ptr, int64_t* t, const int64_t* timestep_map, int32_t step,
+                      int32_t B, void* stream);
+
+/* Count of kernel launches issued through this library by the calling process (for bench.py's
+ * gpu_launches claim). */
+int64_t gd_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GD_B200_H */
