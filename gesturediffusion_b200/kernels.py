@@ -1,0 +1,166 @@
+"""Tensor-level wrappers over the C ABI (one function per entry point of include/gd_b200.h).
+
+These only validate device/dtype/contiguity and unwrap pointers; all arithmetic happens in the
+sm_100a kernels.  Every wrapper raises on CPU tensors -- there is no fallback path.
+"""
+import ctypes as C
+
+import torch
+
+from . import _cabi
+from ._cabi import GD_ACT_GELU_ERF, GD_ACT_NONE, GD_ACT_SILU, GdEpilogue, GdPosteriorArgs  # noqa: F401
+
+
+def _dev(t, dtype=None, name="tensor"):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise _cabi.GdError("%s must be a CUDA tensor (gesturediffusion_b200 has no CPU path)" % name)
+    if dtype is not None and t.dtype != dtype:
+        raise _cabi.GdError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    if not (t.is_contiguous() or (t.dim() == 2 and t.stride(1) == 1)):
+        raise _cabi.GdError("%s must be contiguous (or a row-strided 2-D view)" % name)
+    return t.data_ptr()
+
+
+def epilogue(bias=None, rowtab=None, tab_period=0, tab_offset=0, seqbias=None, seq_rows=0, seq_count=0,
+             residual=None, act=GD_ACT_NONE, rowmap=None, dup=1, dup_row_stride=0, out_f32=None,
+             out_bf16=None, out_t=None, t_s=0, t_t=0, t_skip=0):
+    """Build a GdEpilogue from tensors.  2-D tensors give their row stride as the leading dim."""
+    ep = GdEpilogue()
+    ep.bias = _dev(bias, torch.float32, "bias")
+    ep.rowtab = _dev(rowtab, torch.float32, "rowtab")
+    ep.tab_period, ep.tab_offset = tab_period, tab_offset
+    ep.ld_tab = rowtab.stride(0) if rowtab is not None else 0
+    ep.seqbias = _dev(seqbias, torch.float32, "seqbias")
+    ep.seq_rows, ep.seq_count = seq_rows, seq_count
+    ep.ld_seq = seqbias.stride(0) if seqbias is not None else 0
+    ep.residual = _dev(residual, torch.float32, "residual")
+    ep.ld_res = residual.stride(0) if residual is not None else 0
+    ep.act = act
+    if rowmap is not None:
+        ep.map_t, ep.map_s, ep.map_off = rowmap
+    ep.dup, ep.dup_row_stride = dup, dup_row_stride
+    ep.out_f32 = _dev(out_f32, torch.float32, "out_f32")
+    ep.ld_out = out_f32.stride(0) if out_f32 is not None else 0
+    ep.out_bf16 = _dev(out_bf16, torch.bfloat16, "out_bf16")
+    ep.ld_out_bf16 = out_bf16.stride(0) if out_bf16 is not None else 0
+    ep.out_t = _dev(out_t, torch.float32, "out_t")
+    ep.t_s, ep.t_t, ep.t_skip = t_s, t_t, t_skip
+    return ep
+
+
+def gemm(a, w, ep, M=None, N=None, K=None):
+    """C = A[M,K] @ W[N,K]^T with fused epilogue.  dtype of `a`/`w` picks the kernel:
+    bf16 -> tcgen05/TMEM/TMA, fp32 -> SIMT."""
+    lib = _cabi.load()
+    M = a.shape[0] if M is None else M
+    N = w.shape[0] if N is None else N
+    K = a.shape[1] if K is None else K
+    if a.dtype == torch.bfloat16:
+        rc = lib.gd_gemm_bf16(_dev(a, torch.bfloat16, "A"), a.stride(0), _dev(w, torch.bfloat16, "W"), w.stride(0),
+                              M, N, K, C.byref(ep), _cabi.stream_handle())
+        _cabi.check(rc, "gd_gemm_bf16")
+    else:
+        rc = lib.gd_gemm_f32(_dev(a, torch.float32, "A"), a.stride(0), _dev(w, torch.float32, "W"), w.stride(0),
+                             M, N, K, C.byref(ep), _cabi.stream_handle())
+        _cabi.check(rc, "gd_gemm_f32")
+
+
+def attention(qkv, out, n_seq, S, n_heads, head_dim):
+    lib = _cabi.load()
+    if qkv.dtype == torch.bfloat16:
+        rc = lib.gd_attention_bf16(_dev(qkv, torch.bfloat16, "qkv"), _dev(out, torch.bfloat16, "out"), n_seq, S,
+                                   n_heads, head_dim, _cabi.stream_handle())
+        _cabi.check(rc, "gd_attention_bf16")
+    else:
+        rc = lib.gd_attention_f32(_dev(qkv, torch.float32, "qkv"), _dev(out, torch.float32, "out"), n_seq, S,
+                                  n_heads, head_dim, _cabi.stream_handle())
+        _cabi.check(rc, "gd_attention_f32")
+
+
+def layernorm(x, gamma, beta, out_f32=None, out_bf16=None, eps=1e-5, rows=None):
+    lib = _cabi.load()
+    rows = x.shape[0] if rows is None else rows
+    rc = lib.gd_layernorm(_dev(x, torch.float32, "in"), _dev(gamma, torch.float32, "gamma"),
+                          _dev(beta, torch.float32, "beta"), _dev(out_f32, torch.float32, "out_f32"),
+                          _dev(out_bf16, torch.bfloat16, "out_bf16"), rows, x.shape[-1], eps,
+                          _cabi.stream_handle())
+    _cabi.check(rc, "gd_layernorm")
+
+
+def local_attention(z, rope_cos, rope_sin, x_f32, x_bf16, n_seq, T, d, heads, window=10):
+    lib = _cabi.load()
+    rc = lib.gd_local_attention(_dev(z, torch.float32, "z"), _dev(rope_cos, torch.float32, "rope_cos"),
+                                _dev(rope_sin, torch.float32, "rope_sin"), _dev(x_f32, torch.float32, "x_f32"),
+                                _dev(x_bf16, torch.bfloat16, "x_bf16"), n_seq, T, d, heads, window,
+                                _cabi.stream_handle())
+    _cabi.check(rc, "gd_local_attention")
+
+
+def cond_tokens(t, temb_table, seed_emb, pe0, x_f32, x_bf16, B, n_branch, S, d, coarse_tab=None,
+                coarse_seed=None, coarse_out=None):
+    lib = _cabi.load()
+    rc = lib.gd_cond_tokens(_dev(t, torch.int64, "t"), _dev(temb_table, torch.float32, "temb_table"),
+                            _dev(seed_emb, torch.float32, "seed_emb"), _dev(pe0, torch.float32, "pe0"),
+                            _dev(coarse_tab, torch.float32, "coarse_tab"),
+                            _dev(coarse_seed, torch.float32, "coarse_seed"),
+                            _dev(coarse_out, torch.float32, "coarse_out"), _dev(x_f32, torch.float32, "x_f32"),
+                            _dev(x_bf16, torch.bfloat16, "x_bf16"), B, n_branch, S, d, _cabi.stream_handle())
+    _cabi.check(rc, "gd_cond_tokens")
+
+
+def posterior_step(cond, x_t, coef, step_ptr, B, J, T, uncond=None, scale=None, noise=None, x_prev=None,
+                   pred_xstart=None, mean=None, a_next=None, inpaint_mask=None, inpainted=None,
+                   timestep_map=None, next_t=None, eps_mode=False, clip=False, const_noise=False, seed=0,
+                   sample_base=0):
+    lib = _cabi.load()
+    a = GdPosteriorArgs()
+    a.cond, a.uncond, a.scale = _dev(cond, torch.float32, "cond"), _dev(uncond, torch.float32, "uncond"), \
+        _dev(scale, torch.float32, "scale")
+    a.x_t, a.noise = _dev(x_t, torch.float32, "x_t"), _dev(noise, torch.float32, "noise")
+    a.inpaint_mask, a.inpainted = _dev(inpaint_mask, torch.uint8, "inpaint_mask"), \
+        _dev(inpainted, torch.float32, "inpainted")
+    a.coef, a.n_steps, a.step_ptr = _dev(coef, torch.float32, "coef"), coef.shape[1], \
+        _dev(step_ptr, torch.int32, "step_ptr")
+    a.timestep_map, a.next_t = _dev(timestep_map, torch.int64, "timestep_map"), _dev(next_t, torch.int64, "next_t")
+    a.x_prev, a.pred_xstart, a.mean = _dev(x_prev, torch.float32, "x_prev"), \
+        _dev(pred_xstart, torch.float32, "pred_xstart"), _dev(mean, torch.float32, "mean")
+    if a_next is not None:
+        a.a_next = _dev(a_next, None, "a_next")
+        a.ld_a = a_next.stride(0)
+        a.a_is_bf16 = 1 if a_next.dtype == torch.bfloat16 else 0
+    a.B, a.J, a.T = B, J, T
+    a.eps_mode, a.clip, a.const_noise = int(eps_mode), int(clip), int(const_noise)
+    a.seed, a.sample_base = seed, sample_base
+    rc = lib.gd_posterior_step(C.byref(a), _cabi.stream_handle())
+    _cabi.check(rc, "gd_posterior_step")
+
+
+def pack_rows(src, dst, B, Cc, T, col_off=0):
+    lib = _cabi.load()
+    rc = lib.gd_pack_rows(_dev(src, torch.float32, "src"), _dev(dst, None, "dst"), B, Cc, T, dst.stride(0), col_off,
+                          1 if dst.dtype == torch.bfloat16 else 0, _cabi.stream_handle())
+    _cabi.check(rc, "gd_pack_rows")
+
+
+def q_sample(x0, noise, sqrt_acp, sqrt_1macp, step, out):
+    lib = _cabi.load()
+    rc = lib.gd_q_sample(_dev(x0, torch.float32, "x0"), _dev(noise, torch.float32, "noise"),
+                         _dev(sqrt_acp, torch.float32, "sqrt_acp"), _dev(sqrt_1macp, torch.float32, "sqrt_1macp"),
+                         step, _dev(out, torch.float32, "out"), x0.numel(), _cabi.stream_handle())
+    _cabi.check(rc, "gd_q_sample")
+
+
+def philox_normal(out, B, J, T, seed, sample_base, step):
+    lib = _cabi.load()
+    rc = lib.gd_philox_normal(_dev(out, torch.float32, "out"), B, J, T, seed, sample_base, step,
+                              _cabi.stream_handle())
+    _cabi.check(rc, "gd_philox_normal")
+
+
+def set_loop_state(step_ptr, t, timestep_map, step, B):
+    lib = _cabi.load()
+    rc = lib.gd_set_loop_state(_dev(step_ptr, torch.int32, "step_ptr"), _dev(t, torch.int64, "t"),
+                               _dev(timestep_map, torch.int64, "timestep_map"), step, B, _cabi.stream_handle())
+    _cabi.check(rc, "gd_set_loop_state")

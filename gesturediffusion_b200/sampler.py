@@ -1,0 +1,162 @@
+"""FastLoop: the denoising loop of `p_sample_loop_progressive` (gaussian_diffusion.py:663-730) for
+engine-backed models, with everything per-step kept on the device.
+
+Per step the reference issues ~3000 eager ATen ops, two model calls, a deepcopy of the conditioning
+dict and >= 8 implicit host->device copies.  Here one step is
+    cond_tokens -> input GEMM [-> local attention] -> 8 x (QKV GEMM, attention, out-proj GEMM + residual,
+    LayerNorm, FFN1 GEMM + GELU, FFN2 GEMM + residual, LayerNorm) -> output GEMM (transposed store)
+    -> fused CFG + posterior + noise kernel (which also writes the next step's GEMM operand and
+       advances the device-side step counter / model timesteps)
+captured ONCE into a CUDA graph and replayed `num_timesteps` times; the step index lives in device
+memory, so the host only replays.
+"""
+import torch
+
+from . import kernels as K
+from .diffusion.gaussian_diffusion import ModelMeanType
+
+
+def is_engine_model(model):
+    from .model.base import EngineBackedDenoiser
+    from .model.cfg_sampler import ClassifierFreeSampleModel
+    if isinstance(model, ClassifierFreeSampleModel):
+        return isinstance(model.model, EngineBackedDenoiser)
+    return isinstance(model, EngineBackedDenoiser)
+
+
+class FastLoop:
+    def __init__(self, diffusion, model, device):
+        from .model.cfg_sampler import ClassifierFreeSampleModel
+        self.diffusion = diffusion
+        self.cfg = isinstance(model, ClassifierFreeSampleModel)
+        self.denoiser = model.model if self.cfg else model
+        self.engine = self.denoiser.engine()
+        self.device = self.engine.device
+
+    # -------------------------------------------------------------- per-call state
+    def _state(self, ws, shape, want_pred, has_noise_buf, inpaint):
+        key = ("loop", want_pred, has_noise_buf, inpaint)
+        st = ws.get(key)
+        if st is None:
+            B, J, T = ws["B"], self.engine.J, ws["T"]
+            dev = self.device
+            st = dict(x=torch.zeros(B, J, T, device=dev), scale=torch.ones(B, device=dev),
+                      step=torch.zeros(1, dtype=torch.int32, device=dev), graphs={})
+            if want_pred:
+                st["pred"] = torch.zeros(B, J, T, device=dev)
+            if has_noise_buf:
+                st["noise"] = torch.zeros(B, J, T, device=dev)
+            if inpaint:
+                st["mask"] = torch.zeros(B, J, T, dtype=torch.uint8, device=dev)
+                st["motion"] = torch.zeros(B, J, T, device=dev)
+            ws[key] = st
+        return st
+
+    def _step(self, ws, st, tabs, flags):
+        """One denoising step: model evaluation + fused update (in place on st['x'])."""
+        eng, d = self.engine, self.diffusion
+        B, J, T = ws["B"], eng.J, ws["T"]
+        eng.forward_step(ws)
+        out = ws["OUT"]
+        K.posterior_step(out[:B], st["x"], tabs["coef"], st["step"], B, J, T,
+                         uncond=out[B:] if self.cfg else None, scale=st["scale"] if self.cfg else None,
+                         noise=st.get("noise"), x_prev=st["x"], pred_xstart=st.get("pred"),
+                         a_next=ws["a_in"], inpaint_mask=st.get("mask"), inpainted=st.get("motion"),
+                         timestep_map=tabs["timestep_map"], next_t=ws["t"],
+                         eps_mode=d.model_mean_type == ModelMeanType.EPSILON, clip=flags["clip"],
+                         const_noise=flags["const_noise"], seed=d.seed, sample_base=d.sample_base)
+
+    # -------------------------------------------------------------- the loop
+    def run(self, shape, noise, model_kwargs, clip_denoised, skip_timesteps, init_image, const_noise, step_noise,
+            progress, want_pred, yield_steps):
+        d, eng = self.diffusion, self.engine
+        dev = self.device
+        B, J, F_, T = shape
+        if J * F_ != eng.J:
+            raise ValueError("shape %s does not match the model's %d input features" % (shape, eng.J))
+        y = model_kwargs.get("y", {}) if model_kwargs else {}
+        nb = 2 if self.cfg else 1
+        branches = [False, True] if self.cfg else [bool(y.get("uncond", False))]
+        rng = "inject" if step_noise is not None else d.rng
+        if rng not in ("torch", "philox", "inject"):
+            raise ValueError("diffusion.rng must be 'torch' or 'philox'")
+        inpaint = d._inpaint_of(model_kwargs)
+        n_exec = d.num_timesteps - skip_timesteps
+        if n_exec <= 0:
+            raise ValueError("skip_timesteps leaves no steps to run")
+        if step_noise is not None and len(step_noise) < n_exec:
+            raise ValueError("step_noise needs %d entries" % n_exec)
+
+        with torch.no_grad():
+            ws = eng.workspace(B, T, nb)
+            tabs = d.device_tables(dev)
+            st = self._state(ws, shape, want_pred, rng != "philox", inpaint is not None)
+            eng.prepare_cond(ws, y, branches)
+            if self.cfg:
+                st["scale"].copy_(y["scale"].to(dev, torch.float32).reshape(-1))
+            if inpaint is not None:
+                st["mask"].copy_(inpaint[0].to(dev).reshape(B, eng.J, T).to(torch.uint8))
+                st["motion"].copy_(inpaint[1].to(dev, torch.float32).reshape(B, eng.J, T))
+
+            # initial image (reference :690-703)
+            if noise is not None:
+                img = noise.to(dev, torch.float32).reshape(B, eng.J, T).contiguous()
+            elif rng == "philox":
+                img = torch.empty(B, eng.J, T, device=dev)
+                K.philox_normal(img, B, eng.J, T, d.seed, d.sample_base, d.num_timesteps)
+            else:
+                img = torch.randn(*shape, device=dev).reshape(B, eng.J, T)
+            if skip_timesteps and init_image is None:
+                init_image = torch.zeros(*shape, device=dev)
+            first = n_exec - 1
+            if init_image is not None:
+                q = torch.empty_like(img)
+                K.q_sample(init_image.to(dev, torch.float32).reshape(B, eng.J, T).contiguous(), img,
+                           tabs["sqrt_acp"], tabs["sqrt_1macp"], first, q)
+                img = q
+
+            flags = dict(clip=bool(clip_denoised), const_noise=bool(const_noise))
+            gkey = (flags["clip"], flags["const_noise"], d.model_mean_type, d.seed, d.sample_base, id(tabs["coef"]))
+            graph = None
+            if d.use_cuda_graph:
+                graph = st["graphs"].get(gkey)
+                if graph is None:
+                    # warm-up run outside capture (sets kernel attributes, allocates nothing afterwards)
+                    st["x"].copy_(img)
+                    eng.load_x(ws, st["x"])
+                    K.set_loop_state(st["step"], ws["t"], tabs["timestep_map"], first, B)
+                    self._step(ws, st, tabs, flags)
+                    torch.cuda.current_stream().synchronize()
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        self._step(ws, st, tabs, flags)
+                    st["graphs"][gkey] = graph
+
+            st["x"].copy_(img)
+            eng.load_x(ws, st["x"])
+            K.set_loop_state(st["step"], ws["t"], tabs["timestep_map"], first, B)
+
+            order = range(n_exec)
+            if progress:
+                from tqdm.auto import tqdm
+                order = tqdm(order)
+            for k in order:
+                if rng == "inject":
+                    st["noise"].copy_(step_noise[k].to(dev, torch.float32).reshape(B, eng.J, T))
+                elif rng == "torch":
+                    st["noise"].normal_()
+                if graph is not None:
+                    graph.replay()
+                else:
+                    self._step(ws, st, tabs, flags)
+                last = k == n_exec - 1
+                if yield_steps == "all" or last or (yield_steps is not None and k in yield_steps):
+                    out = {"sample": st["x"].view(B, J, F_, T).clone()}
+                    if want_pred:
+                        out["pred_xstart"] = st["pred"].view(B, J, F_, T).clone()
+                    yield out
+                else:
+                    yield None
+
+    def launches_per_step(self):
+        return self.engine.kernels_per_step() + 1
