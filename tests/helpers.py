@@ -1,0 +1,75 @@
+"""Shared test helpers: golden-fixture access and seeded reconstruction of weights / inputs."""
+import json
+import os
+
+import numpy as np
+import torch
+
+from gesturediffusion_b200.synthetic import make_inputs, make_state_dict, make_step_noise, model_config
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+MODEL_CASES = ["v1_small", "v2_small", "v2_small_text", "v1_humanml", "v1_kit", "v2_gesture", "v2_text"]
+SMALL_MODEL_CASES = ["v1_small", "v2_small", "v2_small_text"]
+CHAIN_CASES = ["chain_v1_small_cfg5", "chain_v2_small_cfg5", "chain_v1_small_uncond4_skip",
+               "chain_v2_small_const_noise", "chain_v1_small_inpaint", "chain_v1_humanml_uncond50",
+               "chain_v2_gesture_cfg50"]
+
+
+def rel_l2(a, b):
+    a, b = a.double().cpu().reshape(-1), b.double().cpu().reshape(-1)
+    return float((a - b).norm() / b.norm())
+
+
+def load_model_case(name):
+    g = np.load(os.path.join(GOLDEN, "model_%s.npz" % name))
+    meta = json.loads(str(g["meta"]))
+    cfg = model_config(**{k: meta["cfg"][k] for k in ("arch", "njoints", "latent_dim", "num_layers", "num_heads",
+                                                      "ff_size", "seed_poses", "use_text")})
+    sd = make_state_dict(cfg, seed=0)
+    x, y = make_inputs(cfg, meta["batch"], meta["frames"])
+    gold = {k: torch.from_numpy(g[k]) for k in ("t", "cond", "uncond", "guided")}
+    return cfg, sd, x, y, gold
+
+
+def load_chain_case(name):
+    g = np.load(os.path.join(GOLDEN, "%s.npz" % name))
+    meta = json.loads(str(g["meta"]))
+    cfg, sd, x, y, _ = load_model_case(meta["case"])
+    extra = meta["extra"]
+    noises = make_step_noise(tuple(x.shape), meta["n_exec"])
+    gen = torch.Generator().manual_seed(99)
+    kwargs = dict(skip_timesteps=extra.get("skip_timesteps", 0), const_noise=extra.get("const_noise", False),
+                  init_image=None)
+    y = dict(y)
+    if extra.get("init_image"):
+        kwargs["init_image"] = torch.randn(*x.shape, generator=gen)
+    if extra.get("inpaint"):
+        y["inpainting_mask"] = torch.rand(*x.shape, generator=gen) < 0.3
+        y["inpainted_motion"] = torch.randn(*x.shape, generator=gen)
+    gold = dict(final=torch.from_numpy(g["final"]), trace_idx=g["trace_idx"].tolist(),
+                trace_sample=torch.from_numpy(g["trace_sample"]), trace_pred=torch.from_numpy(g["trace_pred"]))
+    return cfg, sd, x, y, noises, meta, kwargs, gold
+
+
+def build_product_model(cfg, sd, device, precision):
+    """The package's drop-in model class for `cfg`, loaded with `sd`, on `device`."""
+    from gesturediffusion_b200 import MDM, MDM_Old
+    common = dict(njoints=cfg["njoints"], nfeats=1, pose_rep="rot6d", data_rep="genea_vec",
+                  latent_dim=cfg["latent_dim"], ff_size=cfg["ff_size"], num_layers=cfg["num_layers"],
+                  num_heads=cfg["num_heads"], dropout=0.1, activation="gelu", dataset="genea2023",
+                  cond_mask_prob=0.1, seed_poses=cfg["seed_poses"], mfcc_input=True, use_wav_enc=False,
+                  use_text=cfg["use_text"])
+    if cfg["arch"] == "v2":
+        m = MDM(**common)
+    else:
+        m = MDM_Old(translation=True, glob=True, glob_rot=True, **common)
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not missing and not unexpected
+    m.precision = precision
+    m.eval()
+    return m.to(device)
+
+
+def to_dev(y, device):
+    return {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in y.items()}
