@@ -10,9 +10,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libgd_b200.so")
 
 GD_ACT_NONE, GD_ACT_GELU_ERF, GD_ACT_SILU = 0, 1, 2
+GD_F32, GD_BF16, GD_FP16 = 0, 1, 2
 
 EXPORTED_SYMBOLS = [
-    "gd_abi_version", "gd_last_error", "gd_gemm_bf16", "gd_gemm_f32", "gd_attention_bf16",
+    "gd_abi_version", "gd_last_error", "gd_gemm_h16", "gd_gemm_f32", "gd_attention_h16",
     "gd_attention_f32", "gd_layernorm", "gd_local_attention", "gd_cond_tokens", "gd_posterior_step",
     "gd_pack_rows", "gd_q_sample", "gd_philox_normal", "gd_set_loop_state", "gd_launch_count",
 ]
@@ -30,7 +31,7 @@ class GdEpilogue(C.Structure):
         ("map_t", _i32), ("map_s", _i32), ("map_off", _i32),
         ("dup", _i32), ("dup_row_stride", _i32),
         ("out_f32", _p), ("ld_out", _i32),
-        ("out_bf16", _p), ("ld_out_bf16", _i32),
+        ("out_h16", _p), ("ld_out_h16", _i32), ("h16_fmt", _i32),
         ("out_t", _p), ("t_s", _i32), ("t_t", _i32), ("t_skip", _i32),
     ]
 
@@ -43,7 +44,7 @@ class GdPosteriorArgs(C.Structure):
         ("coef", _p), ("n_steps", _i32), ("step_ptr", _p),
         ("timestep_map", _p), ("next_t", _p),
         ("x_prev", _p), ("pred_xstart", _p), ("mean", _p),
-        ("a_next", _p), ("ld_a", _i32), ("a_is_bf16", _i32),
+        ("a_next", _p), ("ld_a", _i32), ("a_fmt", _i32),
         ("B", _i32), ("J", _i32), ("T", _i32),
         ("eps_mode", _i32), ("clip", _i32), ("const_noise", _i32),
         ("seed", _u64), ("sample_base", _i64),
@@ -71,13 +72,13 @@ def load():
     lib.gd_launch_count.restype = _i64
     E, PA = C.POINTER(GdEpilogue), C.POINTER(GdPosteriorArgs)
     sigs = {
-        "gd_gemm_bf16": [_p, _i32, _p, _i32, _i32, _i32, _i32, E, _p],
+        "gd_gemm_h16": [_p, _i32, _p, _i32, _i32, _i32, _i32, _i32, E, _p],
         "gd_gemm_f32": [_p, _i32, _p, _i32, _i32, _i32, _i32, E, _p],
-        "gd_attention_bf16": [_p, _p, _i32, _i32, _i32, _i32, _p],
+        "gd_attention_h16": [_p, _p, _i32, _i32, _i32, _i32, _i32, _p],
         "gd_attention_f32": [_p, _p, _i32, _i32, _i32, _i32, _p],
-        "gd_layernorm": [_p, _p, _p, _p, _p, _i32, _i32, _f32, _p],
-        "gd_local_attention": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _p],
-        "gd_cond_tokens": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _p],
+        "gd_layernorm": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _f32, _p],
+        "gd_local_attention": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p],
+        "gd_cond_tokens": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _p],
         "gd_posterior_step": [PA, _p],
         "gd_pack_rows": [_p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p],
         "gd_q_sample": [_p, _p, _p, _p, _i32, _p, _i64, _p],
@@ -98,6 +99,17 @@ def check(rc, what):
     if rc != 0:
         msg = load().gd_last_error().decode("utf-8", "replace")
         raise GdError("%s failed (%d): %s" % (what, rc, msg))
+
+
+def fmt_of(t):
+    """gdFmt code of a torch tensor's dtype."""
+    import torch
+    if t is None:
+        return GD_BF16
+    code = {torch.float32: GD_F32, torch.bfloat16: GD_BF16, torch.float16: GD_FP16}.get(t.dtype)
+    if code is None:
+        raise GdError("unsupported dtype %s" % t.dtype)
+    return code
 
 
 def ptr(t):

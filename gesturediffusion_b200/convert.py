@@ -67,7 +67,7 @@ def _convert_diffusion(ref):
     return gd.GaussianDiffusion(**{**kw, "betas": ref.betas})
 
 
-def accelerate(ref_model, ref_diffusion=None, device="cuda", precision="bf16"):
+def accelerate(ref_model, ref_diffusion=None, device="cuda", precision="fp16"):
     """Returns (model, diffusion) engine-backed equivalents of reference instances."""
     model = _convert_model(ref_model, torch.device(device), precision)
     if ref_diffusion is None:

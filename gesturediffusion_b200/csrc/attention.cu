@@ -2,7 +2,7 @@
 // nn.TransformerEncoderLayer (mdm.py:90-96,216): softmax(Q K^T / sqrt(dh)) V per (sequence, head).
 // Input is the packed in_proj output qkv[n_seq*S, 3d] (q | k | v); output out[n_seq*S, d].
 //
-//  * bf16 path: flash-style single pass, 64 queries per CTA (4 warps x 16 rows), 64-key blocks
+//  * 16-bit path (bf16 or fp16, templated): flash-style single pass, 64 queries per CTA (4 warps x 16 rows), 64-key blocks
 //    staged in XOR-swizzled shared memory with cp.async (128-bit), QK^T and PV on mma.sync
 //    m16n8k16 bf16 tensor-core tiles with fp32 accumulation, online softmax with quad shuffles.
 //    (~5% of the step's flops; S <= a few hundred, so one CTA sees the whole K/V of its head.)
@@ -30,11 +30,19 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(s));
 }
-__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+template <bool FP16>
+__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  if constexpr (FP16) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  } else {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
 }
 
 constexpr int AT_BQ = 64, AT_BK = 64, AT_THREADS = 128;
@@ -59,9 +67,9 @@ __device__ __forceinline__ void load_tile(__nv_bfloat16* s, const __nv_bfloat16*
   }
 }
 
-template <int DH>
+template <int DH, bool FP16>
 __global__ void __launch_bounds__(AT_THREADS)
-attention_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int S, int d,
+attention_h16_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int S, int d,
                       float scale_log2e) {
   __shared__ __align__(128) __nv_bfloat16 sQ[AT_BQ * DH];
   __shared__ __align__(128) __nv_bfloat16 sK[AT_BK * DH];
@@ -103,8 +111,8 @@ attention_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __re
       for (int nt = 0; nt < AT_BK / 8; ++nt) {
         uint32_t b[4];
         ldsm_x4(b, sK + swz<DH>(nt * 8 + (lane & 7), kk * 2 + (lane >> 3)));
-        mma_bf16_16816(s[nt], qf[kk], b[0], b[1]);
-        mma_bf16_16816(s[nt], qf[kk + 1], b[2], b[3]);
+        mma_16816<FP16>(s[nt], qf[kk], b[0], b[1]);
+        mma_16816<FP16>(s[nt], qf[kk + 1], b[2], b[3]);
       }
     }
     // mask keys beyond S, online softmax (rows lane/4 and lane/4+8; columns (lane%4)*2 + {0,1})
@@ -146,16 +154,16 @@ attention_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __re
 #pragma unroll
     for (int kk = 0; kk < AT_BK / 16; ++kk) {
       uint32_t pa[4];
-      pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
-      pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
-      pa[2] = pack_bf16x2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-      pa[3] = pack_bf16x2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+      pa[0] = pack_h16x2(s[2 * kk][0], s[2 * kk][1], FP16 ? GD_FP16 : GD_BF16);
+      pa[1] = pack_h16x2(s[2 * kk][2], s[2 * kk][3], FP16 ? GD_FP16 : GD_BF16);
+      pa[2] = pack_h16x2(s[2 * kk + 1][0], s[2 * kk + 1][1], FP16 ? GD_FP16 : GD_BF16);
+      pa[3] = pack_h16x2(s[2 * kk + 1][2], s[2 * kk + 1][3], FP16 ? GD_FP16 : GD_BF16);
 #pragma unroll
       for (int nd = 0; nd < DH / 8; nd += 2) {
         uint32_t b[4];
         ldsm_x4_t(b, sV + swz<DH>(kk * 16 + (lane & 15), nd + (lane >> 4)));
-        mma_bf16_16816(o[nd], pa, b[0], b[1]);
-        mma_bf16_16816(o[nd + 1], pa, b[2], b[3]);
+        mma_16816<FP16>(o[nd], pa, b[0], b[1]);
+        mma_16816<FP16>(o[nd + 1], pa, b[2], b[3]);
       }
     }
   }
@@ -170,8 +178,8 @@ attention_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __re
   __nv_bfloat16* go = out + (size_t)seq * S * d + head * DH + (lane & 3) * 2;
 #pragma unroll
   for (int nd = 0; nd < DH / 8; ++nd) {
-    if (row_a < S) *reinterpret_cast<uint32_t*>(go + (size_t)row_a * d + nd * 8) = pack_bf16x2(o[nd][0] * lrow[0], o[nd][1] * lrow[0]);
-    if (row_b < S) *reinterpret_cast<uint32_t*>(go + (size_t)row_b * d + nd * 8) = pack_bf16x2(o[nd][2] * lrow[1], o[nd][3] * lrow[1]);
+    if (row_a < S) *reinterpret_cast<uint32_t*>(go + (size_t)row_a * d + nd * 8) = pack_h16x2(o[nd][0] * lrow[0], o[nd][1] * lrow[0], FP16 ? GD_FP16 : GD_BF16);
+    if (row_b < S) *reinterpret_cast<uint32_t*>(go + (size_t)row_b * d + nd * 8) = pack_h16x2(o[nd][2] * lrow[1], o[nd][3] * lrow[1], FP16 ? GD_FP16 : GD_BF16);
   }
 }
 
@@ -227,25 +235,30 @@ attention_f32_kernel(const float* __restrict__ qkv, float* __restrict__ out, int
 
 }  // namespace gd
 
-extern "C" int gd_attention_bf16(const void* qkv, void* out, int32_t n_seq, int32_t S, int32_t n_heads,
-                                 int32_t head_dim, void* stream) {
+extern "C" int gd_attention_h16(const void* qkv, void* out, int32_t n_seq, int32_t S, int32_t n_heads,
+                                int32_t head_dim, int32_t fmt, void* stream) {
   using namespace gd;
-  GD_REQUIRE(qkv && out && n_seq > 0 && S > 0 && n_heads > 0, "gd_attention_bf16: bad args");
-  GD_REQUIRE(n_seq <= 65535 && n_heads <= 65535, "gd_attention_bf16: grid too large");
+  GD_REQUIRE(qkv && out && n_seq > 0 && S > 0 && n_heads > 0, "gd_attention_h16: bad args");
+  GD_REQUIRE(n_seq <= 65535 && n_heads <= 65535, "gd_attention_h16: grid too large");
+  GD_REQUIRE(fmt == GD_BF16 || fmt == GD_FP16, "gd_attention_h16: fmt must be GD_BF16 or GD_FP16");
   const int d = n_heads * head_dim;
-  GD_REQUIRE(d % 8 == 0, "gd_attention_bf16: d must be a multiple of 8");
+  GD_REQUIRE(d % 8 == 0, "gd_attention_h16: d must be a multiple of 8");
   const float sl2 = (1.0f / sqrtf((float)head_dim)) * 1.4426950408889634f;
   dim3 grid(ceil_div(S, AT_BQ), n_heads, n_seq);
   cudaStream_t st = (cudaStream_t)stream;
   const __nv_bfloat16* q = (const __nv_bfloat16*)qkv;
   __nv_bfloat16* o = (__nv_bfloat16*)out;
-  if (head_dim == 128) attention_bf16_kernel<128><<<grid, AT_THREADS, 0, st>>>(q, o, S, d, sl2);
-  else if (head_dim == 64) attention_bf16_kernel<64><<<grid, AT_THREADS, 0, st>>>(q, o, S, d, sl2);
-  else if (head_dim == 32) attention_bf16_kernel<32><<<grid, AT_THREADS, 0, st>>>(q, o, S, d, sl2);
+#define GD_ATH(DHV)                                                                              \
+  if (fmt == GD_FP16) attention_h16_kernel<DHV, true><<<grid, AT_THREADS, 0, st>>>(q, o, S, d, sl2); \
+  else attention_h16_kernel<DHV, false><<<grid, AT_THREADS, 0, st>>>(q, o, S, d, sl2);
+  if (head_dim == 128) { GD_ATH(128) }
+  else if (head_dim == 64) { GD_ATH(64) }
+  else if (head_dim == 32) { GD_ATH(32) }
   else {
-    set_error("gd_attention_bf16: head_dim %d not in {32,64,128}", head_dim);
+    set_error("gd_attention_h16: head_dim %d not in {32,64,128}", head_dim);
     return GD_ERR_UNSUPPORTED;
   }
+#undef GD_ATH
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

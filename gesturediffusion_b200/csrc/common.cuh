@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <atomic>
@@ -58,6 +59,21 @@ __device__ __forceinline__ float warp_max(float v) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&p);
+}
+
+// 16-bit packing in the runtime-selected format (GD_BF16 / GD_FP16); fp16 saturates instead of
+// overflowing to inf.
+__device__ __forceinline__ uint32_t pack_h16x2(float lo, float hi, int fmt) {
+  if (fmt == GD_FP16) {
+    lo = fminf(fmaxf(lo, -65504.f), 65504.f);
+    hi = fminf(fmaxf(hi, -65504.f), 65504.f);
+    __half2 p = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&p);
+  }
+  return pack_bf16x2(lo, hi);
+}
+__device__ __forceinline__ uint16_t cvt_h16(float v, int fmt) {
+  return (uint16_t)(pack_h16x2(v, 0.f, fmt) & 0xFFFFu);
 }
 
 __device__ __forceinline__ float gelu_erf(float x) {
@@ -140,22 +156,22 @@ __device__ __forceinline__ void epilogue_row_chunk(const gdEpilogue& ep, int m, 
           if (i < nvalid) o[i] = w[i];
       }
     }
-    if (ep.out_bf16) {
-      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out_bf16) + r * ep.ld_out_bf16 + n0;
+    if (ep.out_h16) {
+      uint16_t* o = reinterpret_cast<uint16_t*>(ep.out_h16) + r * ep.ld_out_h16 + n0;
       if (nvalid == CH && (CH % 8 == 0) && ((((size_t)o) & 15) == 0)) {
 #pragma unroll
         for (int i = 0; i < CH; i += 8) {
           uint4 q;
-          q.x = pack_bf16x2(w[i], w[i + 1]);
-          q.y = pack_bf16x2(w[i + 2], w[i + 3]);
-          q.z = pack_bf16x2(w[i + 4], w[i + 5]);
-          q.w = pack_bf16x2(w[i + 6], w[i + 7]);
+          q.x = pack_h16x2(w[i], w[i + 1], ep.h16_fmt);
+          q.y = pack_h16x2(w[i + 2], w[i + 3], ep.h16_fmt);
+          q.z = pack_h16x2(w[i + 4], w[i + 5], ep.h16_fmt);
+          q.w = pack_h16x2(w[i + 6], w[i + 7], ep.h16_fmt);
           *reinterpret_cast<uint4*>(o + i) = q;
         }
       } else {
 #pragma unroll
         for (int i = 0; i < CH; ++i)
-          if (i < nvalid) o[i] = __float2bfloat16_rn(w[i]);
+          if (i < nvalid) o[i] = cvt_h16(w[i], ep.h16_fmt);
       }
     }
   }

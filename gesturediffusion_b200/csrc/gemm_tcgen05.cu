@@ -1,4 +1,4 @@
-// gemm_tcgen05.cu -- persistent warp-specialised bf16 GEMM for sm_100a.
+// gemm_tcgen05.cu -- persistent warp-specialised 16-bit (bf16 or fp16 operands) GEMM for sm_100a.
 //   C[M,N] = A[M,K] @ W[N,K]^T  (+ fused gdEpilogue), fp32 accumulation in TMEM.
 // Roles (320 threads): warp 0 = TMA producer, warp 1 = UMMA issuer (one elected lane),
 // warps 2..9 = epilogue (TMEM -> registers -> fused epilogue -> global).  The accumulator is
@@ -29,8 +29,8 @@ struct GemmCfg {
 
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                         int M, int N, int K, const gdEpilogue ep) {
+gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                         int M, int N, int K, uint32_t idesc, const gdEpilogue ep) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -90,7 +90,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   } else if (warp == 1) {
     // ------------------------------------------------------------------ UMMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16_f32(kBM, BN);
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
@@ -109,7 +108,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
           for (int k = 0; k < kBK / kUmmaK; ++k) {
             const uint64_t da = ptx::umma_desc_k_sw128(sa + k * kUmmaK * 2);
             const uint64_t db = ptx::umma_desc_k_sw128(sb + k * kUmmaK * 2);
-            ptx::umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_h16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
           }
           ptx::umma_commit(&empty_bar[stage]);               // smem slot reusable when MMAs retire
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -172,7 +171,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2D bf16 row-major [rows, cols] with row stride ld elements; box = [box_rows, 64 cols], SW128.
-static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows) {
+static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
@@ -182,7 +181,7 @@ static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int
   cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
   cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(out, fmt == GD_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -195,37 +194,39 @@ static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int
 static int g_num_sms = 0;
 
 template <int BN>
-static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const gdEpilogue* ep,
-                       cudaStream_t stream) {
+static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int fmt,
+                       const gdEpilogue* ep, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
   static bool attr_set = false;
   if (!attr_set) {
-    GD_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_h16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::kSmemBytes));
     attr_set = true;
   }
   CUtensorMap ta, tw;
-  int rc = make_tmap(&ta, A, M, K, lda, kBM);
+  int rc = make_tmap(&ta, A, M, K, lda, kBM, fmt);
   if (rc) return rc;
-  rc = make_tmap(&tw, W, N, K, ldw, BN);
+  rc = make_tmap(&tw, W, N, K, ldw, BN, fmt);
   if (rc) return rc;
   const int tiles = ceil_div(M, kBM) * ceil_div(N, BN);
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-  gemm_bf16_tcgen05_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tw, M, N, K, *ep);
+  gemm_h16_tcgen05_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(
+      ta, tw, M, N, K, ptx::umma_idesc_h16_f32(kBM, BN, fmt == GD_FP16), *ep);
   GD_LAUNCH_CHECK();
   return GD_OK;
 }
 
 }  // namespace gd
 
-extern "C" int gd_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
-                            const gdEpilogue* ep, void* stream) {
+extern "C" int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                           int32_t fmt, const gdEpilogue* ep, void* stream) {
   using namespace gd;
-  GD_REQUIRE(A && W && ep, "gd_gemm_bf16: null pointer");
-  GD_REQUIRE(M > 0 && N > 0 && K > 0, "gd_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
+  GD_REQUIRE(A && W && ep, "gd_gemm_h16: null pointer");
+  GD_REQUIRE(M > 0 && N > 0 && K > 0, "gd_gemm_h16: bad shape M=%d N=%d K=%d", M, N, K);
+  GD_REQUIRE(fmt == GD_BF16 || fmt == GD_FP16, "gd_gemm_h16: fmt must be GD_BF16 or GD_FP16");
   GD_REQUIRE(lda % 8 == 0 && ldw % 8 == 0 && lda >= K && ldw >= K,
-             "gd_gemm_bf16: lda/ldw must be multiples of 8 and >= K (lda=%d ldw=%d K=%d)", lda, ldw, K);
-  GD_REQUIRE((((uintptr_t)A) & 15) == 0 && (((uintptr_t)W) & 15) == 0, "gd_gemm_bf16: operands must be 16B aligned");
+             "gd_gemm_h16: lda/ldw must be multiples of 8 and >= K (lda=%d ldw=%d K=%d)", lda, ldw, K);
+  GD_REQUIRE((((uintptr_t)A) & 15) == 0 && (((uintptr_t)W) & 15) == 0, "gd_gemm_h16: operands must be 16B aligned");
   int rc = validate_epilogue(ep, M, N);
   if (rc) return rc;
   if (g_num_sms == 0) {
@@ -236,6 +237,6 @@ extern "C" int gd_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t l
   // Tile choice: BN=256 halves A re-reads and epilogue barrier traffic; BN=128 gives finer waves.
   const long tiles256 = (long)ceil_div(M, kBM) * ceil_div(N, 256);
   const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms);
-  if (use256) return launch_gemm<256>(A, lda, W, ldw, M, N, K, ep, (cudaStream_t)stream);
-  return launch_gemm<128>(A, lda, W, ldw, M, N, K, ep, (cudaStream_t)stream);
+  if (use256) return launch_gemm<256>(A, lda, W, ldw, M, N, K, fmt, ep, (cudaStream_t)stream);
+  return launch_gemm<128>(A, lda, W, ldw, M, N, K, fmt, ep, (cudaStream_t)stream);
 }

@@ -1,7 +1,7 @@
 // layernorm.cu -- row LayerNorm (norm1/norm2 of nn.TransformerEncoderLayer, mdm.py:90-96), eps 1e-5.
 // One warp per row, the row held in registers (d <= 1024, d % 128 == 0): 128-bit loads, two-pass
 // mean / variance (sum of squared deviations -- matches the reference's numerics far inside 1e-5),
-// shuffle reductions, fp32 and/or bf16 outputs.  HBM-bound: reads 4*d B/row, writes 4*d + 2*d B/row.
+// shuffle reductions, fp32 and/or 16-bit (bf16/fp16) outputs.  HBM-bound: reads 4*d B/row, writes 4*d + 2*d B/row.
 #include "common.cuh"
 
 namespace gd {
@@ -9,7 +9,7 @@ namespace gd {
 template <int VEC>   // VEC float4 per lane: d = VEC * 128
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* __restrict__ in, const float* __restrict__ gamma, const float* __restrict__ beta,
-                 float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_bf16, int rows, float eps) {
+                 float* __restrict__ out_f32, uint16_t* __restrict__ out_h16, int h16_fmt, int rows, float eps) {
   constexpr int D = VEC * 128;
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -40,28 +40,29 @@ layernorm_kernel(const float* __restrict__ in, const float* __restrict__ gamma, 
     y.z = x[i].z * rstd * g.z + b.z;
     y.w = x[i].w * rstd * g.w + b.w;
     if (out_f32) reinterpret_cast<float4*>(out_f32 + (size_t)row * D)[lane + 32 * i] = y;
-    if (out_bf16) {
+    if (out_h16) {
       uint2 p;
-      p.x = pack_bf16x2(y.x, y.y);
-      p.y = pack_bf16x2(y.z, y.w);
-      reinterpret_cast<uint2*>(out_bf16 + (size_t)row * D)[lane + 32 * i] = p;
+      p.x = pack_h16x2(y.x, y.y, h16_fmt);
+      p.y = pack_h16x2(y.z, y.w, h16_fmt);
+      reinterpret_cast<uint2*>(out_h16 + (size_t)row * D)[lane + 32 * i] = p;
     }
   }
 }
 
 }  // namespace gd
 
-extern "C" int gd_layernorm(const float* in, const float* gamma, const float* beta, float* out_f32, void* out_bf16,
-                            int32_t rows, int32_t d, float eps, void* stream) {
+extern "C" int gd_layernorm(const float* in, const float* gamma, const float* beta, float* out_f32, void* out_h16,
+                            int32_t h16_fmt, int32_t rows, int32_t d, float eps, void* stream) {
   using namespace gd;
-  GD_REQUIRE(in && gamma && beta && (out_f32 || out_bf16), "gd_layernorm: null pointer");
+  GD_REQUIRE(in && gamma && beta && (out_f32 || out_h16), "gd_layernorm: null pointer");
+  GD_REQUIRE(!out_h16 || h16_fmt == GD_BF16 || h16_fmt == GD_FP16, "gd_layernorm: bad h16_fmt");
   GD_REQUIRE(rows > 0 && d % 128 == 0 && d >= 128 && d <= 1024, "gd_layernorm: d=%d must be a multiple of 128 in [128,1024]", d);
   const int warps = 8;
   dim3 grid(ceil_div(rows, warps));
   cudaStream_t st = (cudaStream_t)stream;
-  __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(out_bf16);
+  uint16_t* ob = reinterpret_cast<uint16_t*>(out_h16);
   switch (d / 128) {
-#define GD_LN_CASE(V) case V: layernorm_kernel<V><<<grid, warps * 32, 0, st>>>(in, gamma, beta, out_f32, ob, rows, eps); break;
+#define GD_LN_CASE(V) case V: layernorm_kernel<V><<<grid, warps * 32, 0, st>>>(in, gamma, beta, out_f32, ob, h16_fmt, rows, eps); break;
     GD_LN_CASE(1) GD_LN_CASE(2) GD_LN_CASE(3) GD_LN_CASE(4) GD_LN_CASE(5) GD_LN_CASE(6) GD_LN_CASE(7) GD_LN_CASE(8)
 #undef GD_LN_CASE
   }

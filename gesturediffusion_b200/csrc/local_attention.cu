@@ -6,7 +6,7 @@
 // One CTA per (sequence, head): the [T, e] head slab is read once from HBM (fp32), rotated with the
 // cos/sin tables and kept in shared memory (row stride e+1 -> conflict-free row-parallel reads);
 // each warp then owns query rows: lanes = keys (<= 2*window) for the scores, shuffle softmax,
-// lanes = channels for the PV sum, second rotation at position t+1, coalesced fp32 + bf16 stores
+// lanes = channels for the PV sum, second rotation at position t+1, coalesced fp32 + 16-bit stores
 // straight into rows 1..T of the encoder input.  HBM-bound: 4 B/elem in, 4 (+2) B/elem out.
 // Semantics kept from the reference: the query at in-window offset i of window w attends to all of
 // window w-1 and to offsets 0..i of window w; window 0 has no look-back (its padding keys are masked,
@@ -19,8 +19,8 @@ constexpr int LA_THREADS = 256;
 
 __global__ void __launch_bounds__(LA_THREADS)
 local_attention_kernel(const float* __restrict__ z, const float* __restrict__ rcos, const float* __restrict__ rsin,
-                       float* __restrict__ x_f32, __nv_bfloat16* __restrict__ x_bf16, int T, int d, int e,
-                       int window, float scale) {
+                       float* __restrict__ x_f32, uint16_t* __restrict__ x_h16, int h16_fmt, int T, int d,
+                       int e, int window, float scale) {
   extern __shared__ float sm[];
   const int es = e + 1;
   float* slab = sm;                                   // [T][e+1] rotated q=k=v
@@ -89,7 +89,7 @@ local_attention_kernel(const float* __restrict__ z, const float* __restrict__ rc
       const float p = (ch < half) ? -my[ch + half] : my[ch - half];
       const float y = x * c2[ch] + p * s2[ch];
       if (x_f32) x_f32[orow + ch] = y;
-      if (x_bf16) x_bf16[orow + ch] = __float2bfloat16_rn(y);
+      if (x_h16) x_h16[orow + ch] = cvt_h16(y, h16_fmt);
     }
     __syncwarp();
   }
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(128)
 cond_tokens_kernel(const long long* __restrict__ t, const float* __restrict__ temb, const float* __restrict__ seed_emb,
                    const float* __restrict__ pe0, const float* __restrict__ coarse_tab,
                    const float* __restrict__ coarse_seed, float* __restrict__ coarse_out, float* __restrict__ x_f32,
-                   __nv_bfloat16* __restrict__ x_bf16, int B, int S, int d) {
+                   uint16_t* __restrict__ x_h16, int h16_fmt, int B, int S, int d) {
   const int b = blockIdx.x, c = blockIdx.y;
   const long long tt = t[b];
   const size_t srow = (size_t)(c * B + b);
@@ -107,7 +107,7 @@ cond_tokens_kernel(const long long* __restrict__ t, const float* __restrict__ te
     float v = temb[(size_t)tt * d + i] + seed_emb[srow * d + i];
     if (pe0) v += pe0[i];
     if (x_f32) x_f32[srow * S * d + i] = v;
-    if (x_bf16) x_bf16[srow * S * d + i] = __float2bfloat16_rn(v);
+    if (x_h16) x_h16[srow * S * d + i] = cvt_h16(v, h16_fmt);
     if (coarse_out) coarse_out[srow * d + i] = coarse_tab[(size_t)tt * d + i] + coarse_seed[srow * d + i];
   }
 }
@@ -115,10 +115,11 @@ cond_tokens_kernel(const long long* __restrict__ t, const float* __restrict__ te
 }  // namespace gd
 
 extern "C" int gd_local_attention(const float* z, const float* rope_cos, const float* rope_sin, float* x_f32,
-                                  void* x_bf16, int32_t n_seq, int32_t T, int32_t d, int32_t heads, int32_t window,
-                                  void* stream) {
+                                  void* x_h16, int32_t h16_fmt, int32_t n_seq, int32_t T, int32_t d, int32_t heads,
+                                  int32_t window, void* stream) {
   using namespace gd;
-  GD_REQUIRE(z && rope_cos && rope_sin && (x_f32 || x_bf16), "gd_local_attention: null pointer");
+  GD_REQUIRE(z && rope_cos && rope_sin && (x_f32 || x_h16), "gd_local_attention: null pointer");
+  GD_REQUIRE(!x_h16 || h16_fmt == GD_BF16 || h16_fmt == GD_FP16, "gd_local_attention: bad h16_fmt");
   GD_REQUIRE(n_seq > 0 && n_seq <= 65535 && T > 0 && heads > 0 && d % heads == 0, "gd_local_attention: bad shape");
   GD_REQUIRE(window > 0 && T % window == 0,
              "sequence length must be divisible by window size for local attention (T=%d, window=%d)", T, window);
@@ -133,22 +134,24 @@ extern "C" int gd_local_attention(const float* z, const float* rope_cos, const f
   }
   dim3 grid(heads, n_seq);
   local_attention_kernel<<<grid, LA_THREADS, smem, (cudaStream_t)stream>>>(
-      z, rope_cos, rope_sin, x_f32, (__nv_bfloat16*)x_bf16, T, d, e, window, 1.0f / sqrtf((float)e));
+      z, rope_cos, rope_sin, x_f32, (uint16_t*)x_h16, h16_fmt, T, d, e, window, 1.0f / sqrtf((float)e));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }
 
 extern "C" int gd_cond_tokens(const int64_t* t, const float* temb_table, const float* seed_emb, const float* pe0,
                               const float* coarse_tab, const float* coarse_seed, float* coarse_out, float* x_f32,
-                              void* x_bf16, int32_t B, int32_t n_branch, int32_t S, int32_t d, void* stream) {
+                              void* x_h16, int32_t h16_fmt, int32_t B, int32_t n_branch, int32_t S, int32_t d,
+                              void* stream) {
   using namespace gd;
-  GD_REQUIRE(t && temb_table && seed_emb && (x_f32 || x_bf16 || coarse_out), "gd_cond_tokens: null pointer");
+  GD_REQUIRE(t && temb_table && seed_emb && (x_f32 || x_h16 || coarse_out), "gd_cond_tokens: null pointer");
+  GD_REQUIRE(!x_h16 || h16_fmt == GD_BF16 || h16_fmt == GD_FP16, "gd_cond_tokens: bad h16_fmt");
   GD_REQUIRE(B > 0 && n_branch > 0 && n_branch <= 65535 && S > 0 && d > 0, "gd_cond_tokens: bad shape");
   GD_REQUIRE(!coarse_out || (coarse_tab && coarse_seed), "gd_cond_tokens: coarse_out needs coarse_tab and coarse_seed");
   dim3 grid(B, n_branch);
   cond_tokens_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>((const long long*)t, temb_table, seed_emb, pe0, coarse_tab,
-                                                            coarse_seed, coarse_out, x_f32, (__nv_bfloat16*)x_bf16, B,
-                                                            S, d);
+                                                            coarse_seed, coarse_out, x_f32, (uint16_t*)x_h16, h16_fmt,
+                                                            B, S, d);
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

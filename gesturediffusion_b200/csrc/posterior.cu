@@ -153,8 +153,8 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
       for (int t = w; t < T; t += PS_THREADS / 32) {
         const float v = tile[lane * tstride + t];
         const size_t o = ((size_t)b * T + t) * a.ld_a + j0 + lane;
-        if (a.a_is_bf16) reinterpret_cast<__nv_bfloat16*>(a.a_next)[o] = __float2bfloat16_rn(v);
-        else reinterpret_cast<float*>(a.a_next)[o] = v;
+        if (a.a_fmt == GD_F32) reinterpret_cast<float*>(a.a_next)[o] = v;
+        else reinterpret_cast<uint16_t*>(a.a_next)[o] = cvt_h16(v, a.a_fmt);
       }
     }
   }
@@ -193,7 +193,7 @@ extern "C" int gd_posterior_step(const gdPosteriorArgs* args, void* stream) {
   GD_REQUIRE(a.B > 0 && a.J > 0 && a.T > 0 && a.n_steps > 0, "gd_posterior_step: bad shape");
   GD_REQUIRE(!a.uncond || a.scale, "gd_posterior_step: scale required with uncond");
   GD_REQUIRE(a.x_prev || a.pred_xstart || a.mean, "gd_posterior_step: no output");
-  GD_REQUIRE(!a.a_next || a.ld_a >= a.J, "gd_posterior_step: ld_a < J");
+  GD_REQUIRE(!a.a_next || (a.ld_a >= a.J && a.a_fmt >= GD_F32 && a.a_fmt <= GD_FP16), "gd_posterior_step: ld_a < J or bad a_fmt");
   GD_REQUIRE(a.B <= 65535, "gd_posterior_step: B too large for grid.y");
   if (a.next_t && !g_block_counter) {
     GD_CUDA_OK(cudaMalloc(&g_block_counter, sizeof(uint32_t)));     // one-off, before any capture
@@ -236,9 +236,8 @@ __global__ void q_sample_kernel(const float* x0, const float* noise, const float
 }
 
 // src [B, C, T] fp32 -> dst[(b*T+t)*ld + col_off + c]; 32x32 smem transpose per (b, c-tile, t-tile).
-template <typename OutT>
 __global__ void __launch_bounds__(256)
-pack_rows_kernel(const float* __restrict__ src, OutT* __restrict__ dst, int C, int T, int ld, int col_off) {
+pack_rows_kernel(const float* __restrict__ src, void* __restrict__ dst, int C, int T, int ld, int col_off, int fmt) {
   __shared__ float tile[32][33];
   const int b = blockIdx.z, c0 = blockIdx.y * 32, t0 = blockIdx.x * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -249,7 +248,11 @@ pack_rows_kernel(const float* __restrict__ src, OutT* __restrict__ dst, int C, i
   __syncthreads();
   for (int r = ty; r < 32; r += 8) {
     const int t = t0 + r, c = c0 + tx;
-    if (t < T && c < C) dst[((size_t)b * T + t) * ld + col_off + c] = (OutT)tile[tx][r];
+    if (t < T && c < C) {
+      const size_t o = ((size_t)b * T + t) * ld + col_off + c;
+      if (fmt == GD_F32) reinterpret_cast<float*>(dst)[o] = tile[tx][r];
+      else reinterpret_cast<uint16_t*>(dst)[o] = cvt_h16(tile[tx][r], fmt);
+    }
   }
 }
 
@@ -283,14 +286,12 @@ extern "C" int gd_q_sample(const float* x0, const float* noise, const float* sqr
 }
 
 extern "C" int gd_pack_rows(const float* src, void* dst, int32_t B, int32_t C, int32_t T, int32_t ld, int32_t col_off,
-                            int32_t dst_is_bf16, void* stream) {
+                            int32_t dst_fmt, void* stream) {
   using namespace gd;
   GD_REQUIRE(src && dst && B > 0 && C > 0 && T > 0 && ld >= col_off + C && B <= 65535, "gd_pack_rows: bad args");
   dim3 grid(ceil_div(T, 32), ceil_div(C, 32), B);
-  if (dst_is_bf16)
-    pack_rows_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, C, T, ld, col_off);
-  else
-    pack_rows_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float*)dst, C, T, ld, col_off);
+  GD_REQUIRE(dst_fmt >= GD_F32 && dst_fmt <= GD_FP16, "gd_pack_rows: bad dst_fmt");
+  pack_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, C, T, ld, col_off, dst_fmt);
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

@@ -12,8 +12,10 @@ Data layout in HBM (token-major, sequence-contiguous; the reference's [S,B,d] is
   OUT    fp32 [nb*B, J, T]      model output in the reference layout [.,J,1,T]
 nb = 2 batches the conditional and unconditional branches of classifier-free guidance
 (cfg_sampler.py:23-28) as 2B sequences; branch 0 = cond, branch 1 = uncond.
-`act` is bf16 ("bf16" mode: tcgen05 GEMMs, fp32 accumulate, fp32 residual/LN/softmax statistics)
-or fp32 ("fp32" mode: SIMT kernels, 1e-5 parity runs).
+`act` is fp16 or bf16 ("fp16" / "bf16" modes: tcgen05 kind::f16 GEMMs, fp32 accumulate, fp32
+residual / LayerNorm / softmax statistics; identical speed, fp16 is the default because its 3 extra
+mantissa bits bring the per-step parity from ~4e-3 to ~5e-4 relative L2) or fp32 ("fp32" mode: SIMT
+kernels, 1e-5 parity runs).
 """
 import math
 
@@ -41,7 +43,7 @@ class _Arena:
 
     def materialise(self, device):
         views, bufs = {}, {}
-        for dtype in (torch.bfloat16, torch.float32):
+        for dtype in (torch.float16, torch.bfloat16, torch.float32):
             names = [n for n, (_, dt) in self.items.items() if dt == dtype]
             esz = torch.empty((), dtype=dtype).element_size()
             offs, total = {}, 0
@@ -71,9 +73,9 @@ def _pad_cols(w, ld):
 class DenoiserEngine:
     """Packed weights + workspaces + kernel schedule for one denoiser on one GPU."""
 
-    def __init__(self, state_dict, cfg, device, precision="bf16"):
-        if precision not in ("bf16", "fp32"):
-            raise ValueError("precision must be 'bf16' or 'fp32'")
+    def __init__(self, state_dict, cfg, device, precision="fp16"):
+        if precision not in ("fp16", "bf16", "fp32"):
+            raise ValueError("precision must be 'fp16', 'bf16' or 'fp32'")
         device = torch.device(device)
         if device.type != "cuda":
             raise K._cabi.GdError("DenoiserEngine needs a CUDA device (no CPU path)")
@@ -81,7 +83,8 @@ class DenoiserEngine:
         self.cfg = dict(cfg)
         self.device = device
         self.precision = precision
-        self.act_dtype = torch.bfloat16 if precision == "bf16" else torch.float32
+        self.act_dtype = {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}[precision]
+        self.h16 = precision != "fp32"
         self.arch = cfg["arch"]
         self.d = cfg["latent_dim"]
         self.J = cfg["njoints"]
@@ -200,7 +203,7 @@ class DenoiserEngine:
         ws = dict(B=B, T=T, S=S, nb=nb, R=R)
         ws["a_in"] = buf(B * T, _round_up(self.k_in, 8), dtype=act)
         ws["X32"] = buf(R, d)
-        ws["Xa"] = buf(R, d, dtype=act) if self.precision == "bf16" else ws["X32"]
+        ws["Xa"] = buf(R, d, dtype=act) if self.h16 else ws["X32"]
         ws["QKV"] = buf(R, 3 * d, dtype=act)
         ws["ATT"] = buf(R, d, dtype=act)
         ws["Y32"] = buf(R, d)
@@ -219,7 +222,7 @@ class DenoiserEngine:
 
     def _outs(self, t):
         """Epilogue output kwargs for an `act` buffer."""
-        return dict(out_bf16=t) if t.dtype == torch.bfloat16 else dict(out_f32=t)
+        return dict(out_h16=t) if t.dtype != torch.float32 else dict(out_f32=t)
 
     # ------------------------------------------------------------------ per-call conditioning
     def prepare_cond(self, ws, y, branches):
@@ -270,14 +273,14 @@ class DenoiserEngine:
         B, T, S, nb, R = ws["B"], ws["T"], ws["S"], ws["nb"], ws["R"]
         d, J, w = self.d, self.J, self.w
         X32, Xa = ws["X32"], ws["Xa"]
-        xa_b = Xa if self.precision == "bf16" else None
+        xa_b = Xa if self.h16 else None
         if self.arch == "v1":
             # token 0 = time_embed(pe[t]) + seed_embed + pe[0]   (mdm_old.py:94-99,109-112)
             K.cond_tokens(ws["t"], self.temb_table, ws["seedemb"], self.pe0, X32, xa_b, B, nb, S, d)
             # frames: poseEmbedding(cat(x, mfcc)) + pe[1+t], written to rows 1..T of both branches
             K.gemm(ws["a_in"], w["in.w"],
                    K.epilogue(bias=w["in.b"], rowtab=w["pe"], tab_period=T, tab_offset=1, rowmap=(T, S, 1),
-                              dup=nb, dup_row_stride=B * S, out_f32=X32, out_bf16=xa_b), K=self.k_in)
+                              dup=nb, dup_row_stride=B * S, out_f32=X32, out_h16=xa_b), K=self.k_in)
         else:
             K.cond_tokens(ws["t"], self.temb_table, ws["seedemb"], None, X32, xa_b, B, nb, S, d,
                           coarse_tab=self.coarse_tab, coarse_seed=ws["coarse_seed"], coarse_out=ws["coarse_out"])
@@ -293,10 +296,10 @@ class DenoiserEngine:
             K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(ws["QKV"])), K=d)
             K.attention(ws["QKV"], ws["ATT"], nb * B, S, self.H, dh)
             K.gemm(ws["ATT"], w[p + "o.w"], K.epilogue(bias=w[p + "o.b"], residual=X32, out_f32=ws["Y32"]), K=d)
-            K.layernorm(ws["Y32"], w[p + "norm1.g"], w[p + "norm1.b"], out_f32=X32, out_bf16=xa_b)
+            K.layernorm(ws["Y32"], w[p + "norm1.g"], w[p + "norm1.b"], out_f32=X32, out_h16=xa_b)
             K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
             K.gemm(ws["Hh"], w[p + "f2.w"], K.epilogue(bias=w[p + "f2.b"], residual=X32, out_f32=ws["Y32"]), K=self.F)
-            K.layernorm(ws["Y32"], w[p + "norm2.g"], w[p + "norm2.b"], out_f32=X32, out_bf16=xa_b)
+            K.layernorm(ws["Y32"], w[p + "norm2.g"], w[p + "norm2.b"], out_f32=X32, out_h16=xa_b)
         # OutputProcess + output[1:] + permute to [.,J,1,T] (mdm.py:219-222,372-380)
         K.gemm(Xa, w["out.w"], K.epilogue(bias=w["out.b"], out_t=ws["OUT"], t_s=S, t_t=T, t_skip=1), K=d)
 

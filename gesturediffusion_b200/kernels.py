@@ -8,12 +8,51 @@ import ctypes as C
 import torch
 
 from . import _cabi
-from ._cabi import GD_ACT_GELU_ERF, GD_ACT_NONE, GD_ACT_SILU, GdEpilogue, GdPosteriorArgs  # noqa: F401
+from ._cabi import GD_ACT_GELU_ERF, GD_ACT_NONE, GD_ACT_SILU, GdEpilogue, GdPosteriorArgs, fmt_of  # noqa: F401
+
+H16 = (torch.bfloat16, torch.float16)
+
+# Optional per-launch CUDA-event timing (bench.py's roofline leg / profiles): when PROFILE is a list,
+# every wrapper records (name, meta, start_event, end_event) on the launching stream.
+PROFILE = None
+
+
+class _Timed:
+    def __init__(self, name, **meta):
+        self.name, self.meta = name, meta
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            self.e1.record()
+            PROFILE.append((self.name, self.meta, self.e0, self.e1))
+        return False
+
+
+def profile_summary(records):
+    """Aggregate PROFILE records -> {(name, meta-tuple): (count, total_ms)} (synchronises)."""
+    torch.cuda.synchronize()
+    out = {}
+    for name, meta, e0, e1 in records:
+        key = (name, tuple(sorted(meta.items())))
+        c, t = out.get(key, (0, 0.0))
+        out[key] = (c + 1, t + e0.elapsed_time(e1))
+    return out
 
 
 def _dev(t, dtype=None, name="tensor"):
     if t is None:
         return None
+    if dtype == "h16":
+        if t.dtype not in H16:
+            raise _cabi.GdError("%s must be bfloat16 or float16, got %s" % (name, t.dtype))
+        dtype = None
     if not t.is_cuda:
         raise _cabi.GdError("%s must be a CUDA tensor (gesturediffusion_b200 has no CPU path)" % name)
     if dtype is not None and t.dtype != dtype:
@@ -25,7 +64,7 @@ def _dev(t, dtype=None, name="tensor"):
 
 def epilogue(bias=None, rowtab=None, tab_period=0, tab_offset=0, seqbias=None, seq_rows=0, seq_count=0,
              residual=None, act=GD_ACT_NONE, rowmap=None, dup=1, dup_row_stride=0, out_f32=None,
-             out_bf16=None, out_t=None, t_s=0, t_t=0, t_skip=0):
+             out_h16=None, out_t=None, t_s=0, t_t=0, t_skip=0):
     """Build a GdEpilogue from tensors.  2-D tensors give their row stride as the leading dim."""
     ep = GdEpilogue()
     ep.bias = _dev(bias, torch.float32, "bias")
@@ -43,8 +82,9 @@ def epilogue(bias=None, rowtab=None, tab_period=0, tab_offset=0, seqbias=None, s
     ep.dup, ep.dup_row_stride = dup, dup_row_stride
     ep.out_f32 = _dev(out_f32, torch.float32, "out_f32")
     ep.ld_out = out_f32.stride(0) if out_f32 is not None else 0
-    ep.out_bf16 = _dev(out_bf16, torch.bfloat16, "out_bf16")
-    ep.ld_out_bf16 = out_bf16.stride(0) if out_bf16 is not None else 0
+    ep.out_h16 = _dev(out_h16, "h16", "out_h16")
+    ep.ld_out_h16 = out_h16.stride(0) if out_h16 is not None else 0
+    ep.h16_fmt = fmt_of(out_h16)
     ep.out_t = _dev(out_t, torch.float32, "out_t")
     ep.t_s, ep.t_t, ep.t_skip = t_s, t_t, t_skip
     return ep
@@ -52,16 +92,18 @@ def epilogue(bias=None, rowtab=None, tab_period=0, tab_offset=0, seqbias=None, s
 
 def gemm(a, w, ep, M=None, N=None, K=None):
     """C = A[M,K] @ W[N,K]^T with fused epilogue.  dtype of `a`/`w` picks the kernel:
-    bf16 -> tcgen05/TMEM/TMA, fp32 -> SIMT."""
+    bf16 / fp16 (both operands alike) -> tcgen05/TMEM/TMA, fp32 -> SIMT."""
     lib = _cabi.load()
     M = a.shape[0] if M is None else M
     N = w.shape[0] if N is None else N
     K = a.shape[1] if K is None else K
-    if a.dtype == torch.bfloat16:
-        rc = lib.gd_gemm_bf16(_dev(a, torch.bfloat16, "A"), a.stride(0), _dev(w, torch.bfloat16, "W"), w.stride(0),
-                              M, N, K, C.byref(ep), _cabi.stream_handle())
-        _cabi.check(rc, "gd_gemm_bf16")
+    if a.dtype in H16:
+      with _Timed("gemm_h16", M=M, N=N, K=K):
+        rc = lib.gd_gemm_h16(_dev(a, a.dtype, "A"), a.stride(0), _dev(w, a.dtype, "W"), w.stride(0),
+                             M, N, K, fmt_of(a), C.byref(ep), _cabi.stream_handle())
+        _cabi.check(rc, "gd_gemm_h16")
     else:
+      with _Timed("gemm_f32", M=M, N=N, K=K):
         rc = lib.gd_gemm_f32(_dev(a, torch.float32, "A"), a.stride(0), _dev(w, torch.float32, "W"), w.stride(0),
                              M, N, K, C.byref(ep), _cabi.stream_handle())
         _cabi.check(rc, "gd_gemm_f32")
@@ -69,36 +111,39 @@ def gemm(a, w, ep, M=None, N=None, K=None):
 
 def attention(qkv, out, n_seq, S, n_heads, head_dim):
     lib = _cabi.load()
-    if qkv.dtype == torch.bfloat16:
-        rc = lib.gd_attention_bf16(_dev(qkv, torch.bfloat16, "qkv"), _dev(out, torch.bfloat16, "out"), n_seq, S,
-                                   n_heads, head_dim, _cabi.stream_handle())
-        _cabi.check(rc, "gd_attention_bf16")
-    else:
+    with _Timed("attention", n_seq=n_seq, S=S, H=n_heads, dh=head_dim):
+      if qkv.dtype in H16:
+        rc = lib.gd_attention_h16(_dev(qkv, qkv.dtype, "qkv"), _dev(out, qkv.dtype, "out"), n_seq, S,
+                                  n_heads, head_dim, fmt_of(qkv), _cabi.stream_handle())
+        _cabi.check(rc, "gd_attention_h16")
+      else:
         rc = lib.gd_attention_f32(_dev(qkv, torch.float32, "qkv"), _dev(out, torch.float32, "out"), n_seq, S,
                                   n_heads, head_dim, _cabi.stream_handle())
         _cabi.check(rc, "gd_attention_f32")
 
 
-def layernorm(x, gamma, beta, out_f32=None, out_bf16=None, eps=1e-5, rows=None):
+def layernorm(x, gamma, beta, out_f32=None, out_h16=None, eps=1e-5, rows=None):
     lib = _cabi.load()
     rows = x.shape[0] if rows is None else rows
-    rc = lib.gd_layernorm(_dev(x, torch.float32, "in"), _dev(gamma, torch.float32, "gamma"),
+    with _Timed("layernorm", rows=rows, d=x.shape[-1]):
+      rc = lib.gd_layernorm(_dev(x, torch.float32, "in"), _dev(gamma, torch.float32, "gamma"),
                           _dev(beta, torch.float32, "beta"), _dev(out_f32, torch.float32, "out_f32"),
-                          _dev(out_bf16, torch.bfloat16, "out_bf16"), rows, x.shape[-1], eps,
+                          _dev(out_h16, "h16", "out_h16"), fmt_of(out_h16), rows, x.shape[-1], eps,
                           _cabi.stream_handle())
     _cabi.check(rc, "gd_layernorm")
 
 
-def local_attention(z, rope_cos, rope_sin, x_f32, x_bf16, n_seq, T, d, heads, window=10):
+def local_attention(z, rope_cos, rope_sin, x_f32, x_h16, n_seq, T, d, heads, window=10):
     lib = _cabi.load()
-    rc = lib.gd_local_attention(_dev(z, torch.float32, "z"), _dev(rope_cos, torch.float32, "rope_cos"),
+    with _Timed("local_attention", n_seq=n_seq, T=T, d=d):
+      rc = lib.gd_local_attention(_dev(z, torch.float32, "z"), _dev(rope_cos, torch.float32, "rope_cos"),
                                 _dev(rope_sin, torch.float32, "rope_sin"), _dev(x_f32, torch.float32, "x_f32"),
-                                _dev(x_bf16, torch.bfloat16, "x_bf16"), n_seq, T, d, heads, window,
+                                _dev(x_h16, "h16", "x_h16"), fmt_of(x_h16), n_seq, T, d, heads, window,
                                 _cabi.stream_handle())
     _cabi.check(rc, "gd_local_attention")
 
 
-def cond_tokens(t, temb_table, seed_emb, pe0, x_f32, x_bf16, B, n_branch, S, d, coarse_tab=None,
+def cond_tokens(t, temb_table, seed_emb, pe0, x_f32, x_h16, B, n_branch, S, d, coarse_tab=None,
                 coarse_seed=None, coarse_out=None):
     lib = _cabi.load()
     rc = lib.gd_cond_tokens(_dev(t, torch.int64, "t"), _dev(temb_table, torch.float32, "temb_table"),
@@ -106,7 +151,7 @@ def cond_tokens(t, temb_table, seed_emb, pe0, x_f32, x_bf16, B, n_branch, S, d, 
                             _dev(coarse_tab, torch.float32, "coarse_tab"),
                             _dev(coarse_seed, torch.float32, "coarse_seed"),
                             _dev(coarse_out, torch.float32, "coarse_out"), _dev(x_f32, torch.float32, "x_f32"),
-                            _dev(x_bf16, torch.bfloat16, "x_bf16"), B, n_branch, S, d, _cabi.stream_handle())
+                            _dev(x_h16, "h16", "x_h16"), fmt_of(x_h16), B, n_branch, S, d, _cabi.stream_handle())
     _cabi.check(rc, "gd_cond_tokens")
 
 
@@ -129,18 +174,19 @@ def posterior_step(cond, x_t, coef, step_ptr, B, J, T, uncond=None, scale=None, 
     if a_next is not None:
         a.a_next = _dev(a_next, None, "a_next")
         a.ld_a = a_next.stride(0)
-        a.a_is_bf16 = 1 if a_next.dtype == torch.bfloat16 else 0
+        a.a_fmt = fmt_of(a_next)
     a.B, a.J, a.T = B, J, T
     a.eps_mode, a.clip, a.const_noise = int(eps_mode), int(clip), int(const_noise)
     a.seed, a.sample_base = seed, sample_base
-    rc = lib.gd_posterior_step(C.byref(a), _cabi.stream_handle())
+    with _Timed("posterior_step", B=B, J=J, T=T, cfg=uncond is not None, philox=noise is None):
+      rc = lib.gd_posterior_step(C.byref(a), _cabi.stream_handle())
     _cabi.check(rc, "gd_posterior_step")
 
 
 def pack_rows(src, dst, B, Cc, T, col_off=0):
     lib = _cabi.load()
     rc = lib.gd_pack_rows(_dev(src, torch.float32, "src"), _dev(dst, None, "dst"), B, Cc, T, dst.stride(0), col_off,
-                          1 if dst.dtype == torch.bfloat16 else 0, _cabi.stream_handle())
+                          fmt_of(dst), _cabi.stream_handle())
     _cabi.check(rc, "gd_pack_rows")
 
 

@@ -101,7 +101,7 @@ class EngineBackedDenoiser(nn.Module):
     """forward()/engine plumbing common to both denoisers."""
 
     arch = None
-    precision = "bf16"          # "bf16" (tcgen05) or "fp32" (SIMT parity mode); set before first forward
+    precision = "fp16"          # "fp16" / "bf16" (tcgen05 tensor cores) or "fp32" (SIMT parity mode)
 
     def _engine_cfg(self):
         return dict(arch=self.arch, njoints=self.input_feats, latent_dim=self.latent_dim,

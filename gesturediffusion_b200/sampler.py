@@ -16,6 +16,11 @@ from . import kernels as K
 from .diffusion.gaussian_diffusion import ModelMeanType
 
 
+# launch accounting for bench.py's `gpu_launches` claim: eager launches are counted by the library
+# (gd_launch_count); kernels replayed from a captured graph are counted here.
+STATS = {"graph_replays": 0, "graph_kernels": 0}
+
+
 def is_engine_model(model):
     from .model.base import EngineBackedDenoiser
     from .model.cfg_sampler import ClassifierFreeSampleModel
@@ -147,6 +152,8 @@ class FastLoop:
                     st["noise"].normal_()
                 if graph is not None:
                     graph.replay()
+                    STATS["graph_replays"] += 1
+                    STATS["graph_kernels"] += self.launches_per_step()
                 else:
                     self._step(ws, st, tabs, flags)
                 last = k == n_exec - 1

@@ -36,6 +36,11 @@ typedef enum gdStatus {
 
 typedef enum gdAct { GD_ACT_NONE = 0, GD_ACT_GELU_ERF = 1, GD_ACT_SILU = 2 } gdAct;
 
+/* Element formats of "act" buffers.  The two 16-bit formats run the same tcgen05 kind::f16 path at
+ * the same rate and bytes; GD_FP16 has 3 more mantissa bits (measured per-step parity 5e-4 vs 4e-3
+ * for GD_BF16), GD_BF16 has fp32's exponent range.  fp16 stores saturate to +-65504. */
+typedef enum gdFmt { GD_F32 = 0, GD_BF16 = 1, GD_FP16 = 2 } gdFmt;
+
 /* Fused GEMM epilogue.  For accumulator element (m, n) of  A[M,K] @ W[N,K]^T :
  *   v  = acc + bias[n] + rowtab[((m % tab_period) + tab_offset) * ld_tab + n]
  *   for copy c in [0, dup):                      (dup = 0 or 1 means a single copy)
@@ -43,7 +48,7 @@ typedef enum gdAct { GD_ACT_NONE = 0, GD_ACT_GELU_ERF = 1, GD_ACT_SILU = 2 } gdA
  *     r = rowmap(m) + c * dup_row_stride         rowmap(m) = (m / map_t) * map_s + map_off + m % map_t
  *                                                 (identity when map_t == 0)
  *     w += residual[r * ld_res + n];  w = act(w)
- *     out_f32[r * ld_out + n] = w;  out_bf16[r * ld_out_bf16 + n] = bf16(w)
+ *     out_f32[r * ld_out + n] = w;  out_h16[r * ld_out_h16 + n] = (h16_fmt)(w)
  *   transposed store (out_t != NULL, replaces the row-major stores):
  *     seq = m / t_s, s = m % t_s;  if (s >= t_skip) out_t[((seq * N + n) * t_t) + s - t_skip] = w
  * Every pointer may be NULL to disable that term.  This covers, with one GEMM each:
@@ -60,7 +65,7 @@ typedef struct gdEpilogue {
   int32_t map_t, map_s, map_off;
   int32_t dup, dup_row_stride;
   float* out_f32;        int32_t ld_out;
-  void*  out_bf16;       int32_t ld_out_bf16;
+  void*  out_h16;        int32_t ld_out_h16; int32_t h16_fmt;   /* GD_BF16 or GD_FP16 */
   float* out_t;          int32_t t_s, t_t, t_skip;
 } gdEpilogue;
 
@@ -68,48 +73,49 @@ int gd_abi_version(void);
 const char* gd_last_error(void);                 /* host string, thread-local */
 
 /* Dense projections (replace every aten::addmm on the path: mdm.py:350-356, 151-169, 90-96,
- * 372-380; mdm_old.py:102-118).  bf16: tcgen05.mma (UMMA 128xBNx16, fp32 accumulate in TMEM),
- * operands staged by TMA with 128B swizzle; requires sm_100a, lda/ldw multiples of 8 elements and
- * 16-byte aligned bases.  f32: SIMT fp32 reference-precision path ("fp32 mode" + one-off setup). */
-int gd_gemm_bf16(const void* A, int32_t lda, const void* W, int32_t ldw,
-                 int32_t M, int32_t N, int32_t K, const gdEpilogue* ep, void* stream);
+ * 372-380; mdm_old.py:102-118).  h16: A and W both bf16 or both fp16 (`fmt`), tcgen05.mma (UMMA
+ * 128xBNx16 kind::f16, fp32 accumulate in TMEM), operands staged by TMA with 128B swizzle; requires
+ * sm_100a, lda/ldw multiples of 8 elements and 16-byte aligned bases.  f32: SIMT fp32
+ * reference-precision path ("fp32 mode" + one-off setup). */
+int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ldw,
+                int32_t M, int32_t N, int32_t K, int32_t fmt, const gdEpilogue* ep, void* stream);
 int gd_gemm_f32(const float* A, int32_t lda, const float* W, int32_t ldw,
                 int32_t M, int32_t N, int32_t K, const gdEpilogue* ep, void* stream);
 
 /* Full softmax self-attention of nn.MultiheadAttention inside nn.TransformerEncoderLayer
  * (mdm.py:90-96,216; no mask, scale 1/sqrt(head_dim)).  qkv is the packed in_proj output
  * [n_seq*S, 3*d] (q | k | v, heads contiguous inside each); out is [n_seq*S, d]. */
-int gd_attention_bf16(const void* qkv, void* out, int32_t n_seq, int32_t S, int32_t n_heads,
-                      int32_t head_dim, void* stream);
+int gd_attention_h16(const void* qkv, void* out, int32_t n_seq, int32_t S, int32_t n_heads,
+                     int32_t head_dim, int32_t fmt, void* stream);
 int gd_attention_f32(const float* qkv, float* out, int32_t n_seq, int32_t S, int32_t n_heads,
                      int32_t head_dim, void* stream);
 
 /* LayerNorm (norm1/norm2 of nn.TransformerEncoderLayer, eps 1e-5): rows x d fp32 in,
- * fp32 and/or bf16 out (either may be NULL). */
+ * fp32 and/or 16-bit (`h16_fmt`) out (either may be NULL). */
 int gd_layernorm(const float* in, const float* gamma, const float* beta, float* out_f32,
-                 void* out_bf16, int32_t rows, int32_t d, float eps, void* stream);
+                 void* out_h16, int32_t h16_fmt, int32_t rows, int32_t d, float eps, void* stream);
 
 /* RoPE + causal windowed LocalAttention + second RoPE (mdm.py:176-213; local_attention.py:43-62,
  * 92-172): z [n_seq, T, d] fp32 -> encoder-input rows 1..T of each sequence (token 0 is written by
- * gd_cond_tokens): x_f32 / x_bf16 [n_seq, T+1, d].  q = k = v, `heads` heads of e = d/heads, window
+ * gd_cond_tokens): x_f32 / x_h16 [n_seq, T+1, d].  q = k = v, `heads` heads of e = d/heads, window
  * `window`, one window of look-back; rope_cos/rope_sin are fp32 [T+1, e] tables of
  * cos/sin(cat(pos x inv_freq, pos x inv_freq)) built from the checkpoint's rel_pos.inv_freq: rows 0..T-1
  * rotate the attention input, rows 1..T rotate its output (the cond token sits at position 0).
  * T must be a multiple of `window` (the reference fails otherwise, local_attention.py:100-112). */
 int gd_local_attention(const float* z, const float* rope_cos, const float* rope_sin, float* x_f32,
-                       void* x_bf16, int32_t n_seq, int32_t T, int32_t d, int32_t heads, int32_t window,
-                       void* stream);
+                       void* x_h16, int32_t h16_fmt, int32_t n_seq, int32_t T, int32_t d, int32_t heads,
+                       int32_t window, void* stream);
 
 /* Per-step conditioning token (mdm_old.py:94-99,109-112; mdm.py:130,154-160,197):
  *   tok[c, b, :] = temb_table[t[b], :] + seed_emb[c, b, :] (+ pe0[:])      c in [0, n_branch)
- * written to row (c*B + b) * S of x_f32 / x_bf16 (row stride d), and optionally
+ * written to row (c*B + b) * S of x_f32 / x_h16 (row stride d), and optionally
  *   coarse_out[c*B + b, :] = coarse_tab[t[b], :] + coarse_seed[c, b, :]
  * (the W_c . coa term of project_to_lat, by linearity).  t is int64 [B] of ORIGINAL-schedule
  * timesteps (respace.py:124-129 already applied). */
 int gd_cond_tokens(const int64_t* t, const float* temb_table, const float* seed_emb, const float* pe0,
                    const float* coarse_tab, const float* coarse_seed, float* coarse_out,
-                   float* x_f32, void* x_bf16, int32_t B, int32_t n_branch, int32_t S, int32_t d,
-                   void* stream);
+                   float* x_f32, void* x_h16, int32_t h16_fmt, int32_t B, int32_t n_branch, int32_t S,
+                   int32_t d, void* stream);
 
 /* The fused guidance + posterior + noise update (cfg_sampler.py:28; gaussian_diffusion.py:253-275,
  * 307-311, 354-376, 532-547).  All motion tensors are [B, J, T] fp32 (== [B,J,1,T]).
@@ -124,7 +130,7 @@ int gd_cond_tokens(const int64_t* t, const float* temb_table, const float* seed_
  * Noise: `noise` != NULL reads injected noise (const_noise -> sample 0's noise for all b), else
  * Philox4x32-10 keyed (seed, sample_base + b (or 0 if const_noise), *step_ptr, element) is
  * generated in-kernel.  Optional outputs: pred_xstart, mean, and the next step's GEMM operand
- * a_next[(b*T + t) * ld_a + j] (bf16 or fp32), i.e. InputProcess's permute (mdm.py:350-352) fused
+ * a_next[(b*T + t) * ld_a + j] (format a_fmt: GD_F32 / GD_BF16 / GD_FP16), i.e. InputProcess's permute (mdm.py:350-352) fused
  * into this kernel's store.  If next_t != NULL the kernel also advances the loop state on the
  * device: step_ptr[0] -= 1 and next_t[b] = timestep_map[step-1] (respace.py:124-129). */
 typedef struct gdPosteriorArgs {
@@ -134,7 +140,7 @@ typedef struct gdPosteriorArgs {
   const float* coef; int32_t n_steps; int32_t* step_ptr;
   const int64_t* timestep_map; int64_t* next_t;
   float* x_prev; float* pred_xstart; float* mean;
-  void* a_next; int32_t ld_a; int32_t a_is_bf16;
+  void* a_next; int32_t ld_a; int32_t a_fmt;
   int32_t B, J, T;
   int32_t eps_mode, clip, const_noise;
   uint64_t seed; int64_t sample_base;
@@ -142,9 +148,9 @@ typedef struct gdPosteriorArgs {
 int gd_posterior_step(const gdPosteriorArgs* args, void* stream);
 
 /* InputProcess's permute for the first step / standalone forward (mdm.py:350-352, mdm_old.py:102-103):
- * src [B, C, T] fp32 -> dst[(b*T + t) * ld + col_off + c] (bf16 or fp32). */
+ * src [B, C, T] fp32 -> dst[(b*T + t) * ld + col_off + c] (dst_fmt: GD_F32 / GD_BF16 / GD_FP16). */
 int gd_pack_rows(const float* src, void* dst, int32_t B, int32_t C, int32_t T, int32_t ld,
-                 int32_t col_off, int32_t dst_is_bf16, void* stream);
+                 int32_t col_off, int32_t dst_fmt, void* stream);
 
 /* q_sample (gaussian_diffusion.py:233-251) for skip_timesteps/init_image:
  * out = a[step]*x0 + b[step]*noise with a/b fp32 device tables. */

@@ -1,0 +1,280 @@
+"""GPU: every CUDA kernel, called through the C ABI, against a plain torch restatement of the same op
+on the same seeded inputs (fp64 on the GPU for the reference value).  Tolerances: fp32 kernels 1e-5
+relative L2 (north star 'fp32 mode'), 16-bit (bf16 / fp16) tensor-core kernels against the reference evaluated on
+the SAME bf16-rounded operands with wide accumulation (operand rounding itself is a model-level effect
+measured in test_gpu_model.py)."""
+import math
+
+import pytest
+import torch
+
+from helpers import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def _K():
+    from gesturediffusion_b200 import kernels
+    return kernels
+
+
+TDT = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}
+H16_ROUND = {"bf16": 3e-3, "fp16": 4e-4}        # relative L2 of one 16-bit output rounding (worst case)
+
+
+def _gelu(x):
+    return 0.5 * x * (1 + torch.erf(x / math.sqrt(2)))
+
+
+# ------------------------------------------------------------------ GEMMs
+GEMM_SHAPES = [(128, 128, 64), (256, 512, 512), (1000, 1536, 512), (197, 263, 512), (392, 512, 289),
+               (3000, 1024, 512), (40000, 512, 1024), (60, 24, 24), (130, 384, 128)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
+def test_gemm_bias(cuda_device, M, N, K, dtype):
+    Kn = _K()
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N)
+    ld = (K + 7) // 8 * 8
+    a = torch.zeros(M, ld, device="cuda")
+    w = torch.zeros(N, ld, device="cuda")
+    a[:, :K] = torch.randn(M, K, device="cuda", generator=g)
+    w[:, :K] = torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K)
+    bias = torch.randn(N, device="cuda", generator=g)
+    a, w = a.to(TDT[dtype]), w.to(TDT[dtype])
+    ref = a[:, :K].double() @ w[:, :K].double().T + bias.double()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, out_f32=out), K=K)
+    torch.cuda.synchronize()
+    assert rel_l2(out, ref) < (2e-6 if dtype == "fp32" else 1e-5)     # fp32 accumulation in both
+
+
+@pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
+def test_gemm_epilogue_residual_gelu_h16out(cuda_device, dtype):
+    Kn = _K()
+    M, N, K = 700, 1024, 512
+    g = torch.Generator(device="cuda").manual_seed(5)
+    a = torch.randn(M, K, device="cuda", generator=g)
+    w = torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K)
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    a, w = a.to(TDT[dtype]), w.to(TDT[dtype])
+    base = a.double() @ w.double().T + bias.double()
+    out32 = torch.empty(M, N, device="cuda")
+    hdt = torch.float16 if dtype == "fp16" else torch.bfloat16
+    outb = torch.empty(M, N, device="cuda", dtype=hdt)
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, residual=res, out_f32=out32))
+    assert rel_l2(out32, base + res.double()) < 1e-5
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, act=Kn.GD_ACT_GELU_ERF, out_f32=out32, out_h16=outb))
+    assert rel_l2(out32, _gelu(base)) < 1e-5
+    assert rel_l2(outb.float(), _gelu(base)) < H16_ROUND["fp16" if dtype == "fp16" else "bf16"]   # output rounding only
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, act=Kn.GD_ACT_SILU, out_f32=out32))
+    assert rel_l2(out32, base * torch.sigmoid(base)) < 1e-5
+
+
+@pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
+def test_gemm_epilogue_rowmap_dup_tables_transposed(cuda_device, dtype):
+    """The input-projection epilogue (row remap to rows 1..T of each sequence, duplicated per CFG branch,
+    + positional table + per-sequence bias) and the output-projection epilogue (transposed [.,J,T] store
+    skipping token 0)."""
+    Kn = _K()
+    B, T, d, J, nb = 3, 20, 128, 24, 2
+    S = T + 1
+    g = torch.Generator(device="cuda").manual_seed(11)
+    a = torch.randn(B * T, 32, device="cuda", generator=g)
+    w = torch.randn(d, 32, device="cuda", generator=g) / 5
+    bias = torch.randn(d, device="cuda", generator=g)
+    tab = torch.randn(50, d, device="cuda", generator=g)
+    seqb = torch.randn(nb * B, d, device="cuda", generator=g)
+    a, w = a.to(TDT[dtype]), w.to(TDT[dtype])
+    X = torch.zeros(nb * B * S, d, device="cuda")
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, rowtab=tab, tab_period=T, tab_offset=1, seqbias=seqb, seq_rows=T,
+                              seq_count=B, rowmap=(T, S, 1), dup=nb, dup_row_stride=B * S, out_f32=X))
+    base = (a.double() @ w.double().T + bias.double()).view(B, T, d) + tab[1:T + 1].double()
+    ref = torch.zeros(nb, B, S, d, dtype=torch.float64, device="cuda")
+    for c in range(nb):
+        ref[c, :, 1:] = base + seqb[c * B:(c + 1) * B].double().unsqueeze(1)
+    assert rel_l2(X, ref.view(-1, d)) < 1e-5
+    assert float(X.view(nb, B, S, d)[:, :, 0].abs().max()) == 0.0      # token-0 rows untouched
+
+    xin = torch.randn(nb * B * S, d, device="cuda", generator=g)
+    wo = torch.randn(J, d, device="cuda", generator=g) / 10
+    bo = torch.randn(J, device="cuda", generator=g)
+    xin, wo = xin.to(TDT[dtype]), wo.to(TDT[dtype])
+    out = torch.full((nb * B, J, T), float("nan"), device="cuda")
+    Kn.gemm(xin, wo, Kn.epilogue(bias=bo, out_t=out, t_s=S, t_t=T, t_skip=1))
+    ref = (xin.double() @ wo.double().T + bo.double()).view(nb * B, S, J)[:, 1:].transpose(1, 2)
+    assert rel_l2(out, ref) < 1e-5
+
+
+# ------------------------------------------------------------------ attention / LN
+@pytest.mark.parametrize("n_seq,S,H,dh", [(3, 21, 4, 32), (2, 121, 4, 128), (2, 197, 4, 128), (1, 64, 2, 64),
+                                         (2, 301, 4, 128)])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
+def test_attention(cuda_device, n_seq, S, H, dh, dtype):
+    Kn = _K()
+    d = H * dh
+    g = torch.Generator(device="cuda").manual_seed(S)
+    qkv = torch.randn(n_seq * S, 3 * d, device="cuda", generator=g)
+    tdt = TDT[dtype]
+    qkv = qkv.to(tdt)
+    out = torch.zeros(n_seq * S, d, device="cuda", dtype=tdt)
+    Kn.attention(qkv, out, n_seq, S, H, dh)
+    q, k, v = qkv.double().view(n_seq, S, 3, H, dh).permute(2, 0, 3, 1, 4)
+    ref = torch.softmax(q @ k.transpose(-1, -2) / math.sqrt(dh), dim=-1) @ v
+    ref = ref.permute(0, 2, 1, 3).reshape(n_seq * S, d)
+    # 16-bit: P and O are rounded to the 16-bit format
+    assert rel_l2(out.float(), ref) < {"fp32": 2e-6, "bf16": 6e-3, "fp16": 8e-4}[dtype]
+
+
+@pytest.mark.parametrize("rows,d", [(1, 128), (1000, 512), (777, 1024)])
+def test_layernorm(cuda_device, rows, d):
+    Kn = _K()
+    g = torch.Generator(device="cuda").manual_seed(rows)
+    x = torch.randn(rows, d, device="cuda", generator=g) * 3 + 1
+    gamma = torch.randn(d, device="cuda", generator=g)
+    beta = torch.randn(d, device="cuda", generator=g)
+    o32 = torch.empty_like(x)
+    ref = torch.nn.functional.layer_norm(x.double(), (d,), gamma.double(), beta.double(), 1e-5)
+    for hdt in (torch.bfloat16, torch.float16):
+        ob = torch.empty(rows, d, device="cuda", dtype=hdt)
+        Kn.layernorm(x, gamma, beta, out_f32=o32, out_h16=ob)
+        assert rel_l2(o32, ref) < 1e-6
+        assert torch.equal(ob, o32.to(hdt))
+
+
+# ------------------------------------------------------------------ local attention + RoPE
+@pytest.mark.parametrize("n_seq,T,d,heads", [(3, 20, 128, 8), (2, 120, 512, 8), (1, 600, 512, 8), (2, 10, 128, 8)])
+def test_local_attention_rope(cuda_device, n_seq, T, d, heads):
+    from oracle.model_oracle import local_window_attention, rope_angles, rope_apply
+    Kn = _K()
+    e = d // heads
+    g = torch.Generator().manual_seed(T)
+    z = torch.randn(n_seq, T, d, generator=g)
+    ang = rope_angles(T + 1, e, torch.float64)
+    zh = z.double().view(n_seq, T, heads, e).transpose(1, 2).reshape(n_seq * heads, T, e)
+    oh = local_window_attention(rope_apply(zh, ang[:T]), 10)
+    oh = rope_apply(oh, ang[1:T + 1])
+    ref = oh.view(n_seq, heads, T, e).transpose(1, 2).reshape(n_seq, T, d)
+    x32 = torch.zeros(n_seq, T + 1, d, device="cuda")
+    xb = torch.zeros(n_seq, T + 1, d, device="cuda", dtype=torch.float16)
+    angf = rope_angles(T + 1, e, torch.float32)
+    Kn.local_attention(z.cuda(), angf.cos().cuda().contiguous(), angf.sin().cuda().contiguous(), x32, xb,
+                       n_seq, T, d, heads, 10)
+    assert rel_l2(x32[:, 1:], ref) < 1e-5
+    assert float(x32[:, 0].abs().max()) == 0.0
+    assert torch.equal(xb, x32.half())
+
+
+def test_local_attention_rejects_bad_length(cuda_device):
+    from gesturediffusion_b200 import _cabi
+    Kn = _K()
+    z = torch.zeros(1, 25, 128, device="cuda")
+    tab = torch.zeros(26, 16, device="cuda")
+    with pytest.raises(_cabi.GdError, match="divisible by window size"):
+        Kn.local_attention(z, tab, tab, torch.zeros(1, 26, 128, device="cuda"), None, 1, 25, 128, 8, 10)
+
+
+# ------------------------------------------------------------------ fused posterior step
+def _coef(n):
+    from gesturediffusion_b200 import create_gaussian_diffusion
+    d = create_gaussian_diffusion(timestep_respacing=[n])
+    return d, d.device_tables(torch.device("cuda"))
+
+
+@pytest.mark.parametrize("B,J,T", [(3, 24, 20), (2, 263, 196), (2, 498, 120), (1, 7, 13)])
+@pytest.mark.parametrize("step", [0, 3])
+def test_posterior_step_injected_noise(cuda_device, B, J, T, step):
+    Kn = _K()
+    d, tabs = _coef(5)
+    g = torch.Generator(device="cuda").manual_seed(B * 100 + T)
+    c, u, x, nz = (torch.randn(B, J, T, device="cuda", generator=g) for _ in range(4))
+    scale = torch.rand(B, device="cuda", generator=g) * 3
+    tabs["step"].fill_(step)
+    xp, x0, mean = (torch.empty(B, J, T, device="cuda") for _ in range(3))
+    ld = (J + 26 + 7) // 8 * 8
+    a_next = torch.zeros(B * T, ld, device="cuda", dtype=torch.float16 if step else torch.bfloat16)
+    Kn.posterior_step(c, x, tabs["coef"], tabs["step"], B, J, T, uncond=u, scale=scale, noise=nz, x_prev=xp,
+                      pred_xstart=x0, mean=mean, a_next=a_next)
+    r0 = u + scale.view(-1, 1, 1) * (c - u)
+    c1 = torch.tensor(d.posterior_mean_coef1[step]).float().cuda()
+    c2 = torch.tensor(d.posterior_mean_coef2[step]).float().cuda()
+    lv = torch.tensor(d.posterior_log_variance_clipped[step]).float().cuda()
+    rmean = c1 * r0 + c2 * x
+    rxp = rmean + (0.0 if step == 0 else 1.0) * torch.exp(0.5 * lv) * nz
+    assert rel_l2(x0, r0) < 1e-6 and rel_l2(mean, rmean) < 1e-6 and rel_l2(xp, rxp) < 1e-6
+    assert torch.equal(a_next[:, :J].view(B, T, J), xp.transpose(1, 2).to(a_next.dtype))
+    assert float(a_next[:, J:].float().abs().max()) == 0.0
+    assert int(tabs["step"].item()) == step                      # no loop-state update requested
+
+
+def test_posterior_step_inpaint_clip_eps_const_noise_and_loop_state(cuda_device):
+    Kn = _K()
+    d, tabs = _coef(6)
+    B, J, T = 4, 24, 20
+    g = torch.Generator(device="cuda").manual_seed(1)
+    c, x, nz, motion = (torch.randn(B, J, T, device="cuda", generator=g) for _ in range(4))
+    mask = (torch.rand(B, J, T, device="cuda", generator=g) < 0.4)
+    step = 4
+    tabs["step"].fill_(step)
+    tnext = torch.zeros(B, dtype=torch.int64, device="cuda")
+    xp, x0 = torch.empty_like(x), torch.empty_like(x)
+    Kn.posterior_step(c, x, tabs["coef"], tabs["step"], B, J, T, noise=nz, x_prev=xp, pred_xstart=x0,
+                      inpaint_mask=mask.to(torch.uint8), inpainted=motion, clip=True, const_noise=True,
+                      timestep_map=tabs["timestep_map"], next_t=tnext)
+    r0 = torch.where(mask, motion, c).clamp(-1, 1)
+    f = lambda a: torch.tensor(a[step]).float().cuda()
+    rxp = f(d.posterior_mean_coef1) * r0 + f(d.posterior_mean_coef2) * x + \
+        torch.exp(0.5 * f(d.posterior_log_variance_clipped)) * nz[:1]
+    assert rel_l2(x0, r0) < 1e-6 and rel_l2(xp, rxp) < 1e-6
+    assert int(tabs["step"].item()) == step - 1
+    assert tnext.tolist() == [d.timestep_map[step - 1]] * B
+    # epsilon parameterisation
+    tabs["step"].fill_(2)
+    Kn.posterior_step(c, x, tabs["coef"], tabs["step"], B, J, T, pred_xstart=x0, eps_mode=True)
+    r = torch.tensor(d.sqrt_recip_alphas_cumprod[2]).float().cuda() * x - \
+        torch.tensor(d.sqrt_recipm1_alphas_cumprod[2]).float().cuda() * c
+    assert rel_l2(x0, r) < 1e-6
+
+
+def test_philox_noise_statistics_and_shard_invariance(cuda_device):
+    """In-kernel Philox: N(0,1) moments, determinism, and the per-sample stream does not depend on how
+    the batch is sharded (sample_base) -- the multi-GPU invariance of SURVEY 8.5."""
+    Kn = _K()
+    B, J, T = 8, 263, 196
+    full = torch.empty(B, J, T, device="cuda")
+    Kn.philox_normal(full, B, J, T, 1234, 0, 17)
+    assert abs(float(full.mean())) < 5e-3 and abs(float(full.std()) - 1) < 5e-3
+    assert abs(float((full ** 4).mean()) - 3.0) < 0.05
+    part = torch.empty(3, J, T, device="cuda")
+    Kn.philox_normal(part, 3, J, T, 1234, 5, 17)
+    assert torch.equal(part, full[5:8])
+    other = torch.empty(B, J, T, device="cuda")
+    Kn.philox_normal(other, B, J, T, 1234, 0, 18)
+    assert float((other - full).abs().max()) > 1.0
+    # the fused kernel draws the same values: x_prev - mean == sigma * z
+    d, tabs = _coef(50)
+    tabs["step"].fill_(17)
+    c, x = torch.zeros(B, J, T, device="cuda"), torch.zeros(B, J, T, device="cuda")
+    xp = torch.empty_like(x)
+    Kn.posterior_step(c, x, tabs["coef"], tabs["step"], B, J, T, x_prev=xp, seed=1234, sample_base=0)
+    sigma = math.exp(0.5 * d.posterior_log_variance_clipped[17])
+    assert rel_l2(xp, full * sigma) < 1e-6
+
+
+def test_pack_rows_and_q_sample(cuda_device):
+    Kn = _K()
+    B, C, T = 3, 26, 50
+    src = torch.randn(B, C, T, device="cuda")
+    for ddt in (torch.bfloat16, torch.float16, torch.float32):
+        dst = torch.zeros(B * T, 64, device="cuda", dtype=ddt)
+        Kn.pack_rows(src, dst, B, C, T, col_off=30)
+        assert torch.equal(dst[:, 30:56].view(B, T, C), src.transpose(1, 2).to(ddt))
+        assert float(dst[:, :30].float().abs().max()) == 0.0
+    d, tabs = _coef(10)
+    x0, nz = torch.randn(1000, device="cuda"), torch.randn(1000, device="cuda")
+    out = torch.empty(1000, device="cuda")
+    Kn.q_sample(x0, nz, tabs["sqrt_acp"], tabs["sqrt_1macp"], 7, out)
+    ref = float(d.sqrt_alphas_cumprod[7]) * x0.double() + float(d.sqrt_one_minus_alphas_cumprod[7]) * nz.double()
+    assert rel_l2(out, ref) < 1e-6

@@ -42,7 +42,7 @@ def test_same_seed_same_init_as_reference(arch):
 
 def test_cpu_model_refuses_to_run():
     cfg, sd, x, y, gold = load_model_case("v1_small")
-    m = build_product_model(cfg, sd, "cpu", "bf16")
+    m = build_product_model(cfg, sd, "cpu", "fp16")
     with pytest.raises(_cabi.GdError):
         m(x, gold["t"], y)
     d = create_gaussian_diffusion(timestep_respacing=[4])
@@ -52,7 +52,7 @@ def test_cpu_model_refuses_to_run():
 
 def test_cfg_wrapper_contract():
     cfg, sd, x, y, gold = load_model_case("v1_small")
-    m = build_product_model(cfg, sd, "cpu", "bf16")
+    m = build_product_model(cfg, sd, "cpu", "fp16")
     w = ClassifierFreeSampleModel(m)
     assert w.njoints == m.njoints and w.nfeats == m.nfeats and w.data_rep == m.data_rep and w.rot2xyz is m.rot2xyz
     assert len(list(w.parameters())) == len(list(m.parameters()))
