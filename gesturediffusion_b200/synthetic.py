@@ -95,3 +95,23 @@ def make_inputs(cfg, batch, frames, seed=1234, guidance=2.5, device="cpu"):
 def make_step_noise(shape, n_steps, seed=4321):
     g = torch.Generator().manual_seed(seed)
     return [torch.randn(*shape, generator=g) for _ in range(n_steps)]
+
+
+def build_model(cfg, state_dict, device, precision="fp16"):
+    """The package's drop-in denoiser class for `cfg`, loaded with `state_dict`, on `device`."""
+    from .model.mdm import MDM
+    from .model.mdm_old import MDM_Old
+    common = dict(njoints=cfg["njoints"], nfeats=1, pose_rep="rot6d", data_rep="genea_vec",
+                  latent_dim=cfg["latent_dim"], ff_size=cfg["ff_size"], num_layers=cfg["num_layers"],
+                  num_heads=cfg["num_heads"], dropout=0.1, activation="gelu", dataset="genea2023",
+                  cond_mask_prob=0.1, seed_poses=cfg["seed_poses"], mfcc_input=True, use_wav_enc=False,
+                  use_text=cfg["use_text"])
+    if cfg["arch"] == "v2":
+        m = MDM(**common)
+    else:
+        m = MDM_Old(translation=True, glob=True, glob_rot=True, **common)
+    missing, unexpected = m.load_state_dict(state_dict, strict=False)
+    assert not missing and not unexpected, (missing, unexpected)
+    m.precision = precision
+    m.eval()
+    return m.to(device)

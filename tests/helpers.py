@@ -54,21 +54,8 @@ def load_chain_case(name):
 
 def build_product_model(cfg, sd, device, precision):
     """The package's drop-in model class for `cfg`, loaded with `sd`, on `device`."""
-    from gesturediffusion_b200 import MDM, MDM_Old
-    common = dict(njoints=cfg["njoints"], nfeats=1, pose_rep="rot6d", data_rep="genea_vec",
-                  latent_dim=cfg["latent_dim"], ff_size=cfg["ff_size"], num_layers=cfg["num_layers"],
-                  num_heads=cfg["num_heads"], dropout=0.1, activation="gelu", dataset="genea2023",
-                  cond_mask_prob=0.1, seed_poses=cfg["seed_poses"], mfcc_input=True, use_wav_enc=False,
-                  use_text=cfg["use_text"])
-    if cfg["arch"] == "v2":
-        m = MDM(**common)
-    else:
-        m = MDM_Old(translation=True, glob=True, glob_rot=True, **common)
-    missing, unexpected = m.load_state_dict(sd, strict=False)
-    assert not missing and not unexpected
-    m.precision = precision
-    m.eval()
-    return m.to(device)
+    from gesturediffusion_b200.synthetic import build_model
+    return build_model(cfg, sd, device, precision)
 
 
 def to_dev(y, device):
