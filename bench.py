@@ -130,7 +130,7 @@ def workload_name(args, cfg, B, T, D, use_cfg):
 
 
 # ------------------------------------------------------------------------------------------ CPU oracle timing
-def cpu_oracle_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads):
+def cpu_oracle_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads, min_seconds=12.0):
     """Times the CPU oracle port (oracle/: the reference's algorithm restated on torch CPU ops, pinned to the
     reference by tests/golden) on a bounded sample; returns (frames/s for a D-step chain, ms/denoise-step,
     description).  Linear extrapolation in batch and steps is stated in the description."""
@@ -144,13 +144,17 @@ def cpu_oracle_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads):
     x, y = make_inputs(cfg, sample_b, T, guidance=GUIDANCE)
     noises = make_step_noise(tuple(x.shape), sample_steps)
     od.p_sample_loop(model, x, y, noises[:1], skip_timesteps=D - 1)           # warm-up: one step
-    t0 = time.perf_counter()
-    od.p_sample_loop(model, x, y, noises, skip_timesteps=D - sample_steps)
-    dt = time.perf_counter() - t0
-    ms_step = dt / sample_steps * 1e3
+    reps, dt = 0, 0.0
+    while dt < min_seconds or reps == 0:                                       # bounded sample: >= min_seconds of CPU work
+        t0 = time.perf_counter()
+        od.p_sample_loop(model, x, y, noises, skip_timesteps=D - sample_steps)
+        dt += time.perf_counter() - t0
+        reps += 1
+    ms_step = dt / (reps * sample_steps) * 1e3
     fps = sample_b * T / (ms_step * 1e-3 * D)
-    desc = ("oracle port (torch CPU fp32), batch %d x %d denoise steps timed (%.1f s), %s; frames/s extrapolated "
-            "linearly to %d steps" % (sample_b, sample_steps, dt, "CFG" if use_cfg else "no CFG", D))
+    desc = ("oracle port (torch CPU fp32, %d threads), batch %d x %d denoise steps x %d repeats timed (%.1f s), %s; "
+            "frames/s = batch*frames / (ms_per_denoise_step * %d steps)"
+            % (threads, sample_b, sample_steps, reps, dt, "CFG" if use_cfg else "no CFG", D))
     return fps, ms_step, desc
 
 
@@ -164,7 +168,7 @@ def run_reference(args):
     D = args.denoise_steps
     use_cfg = not args.no_cfg
     threads = os.cpu_count() or 1
-    sample_b, sample_steps = (4, 3) if B > 1 else (1, 10)
+    sample_b, sample_steps = (min(B, 16), 10) if B > 1 else (1, D)
     vals, ms = [], []
     for i in range(args.warmup + args.steps):
         fps, ms_step, desc = cpu_oracle_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads)
@@ -343,7 +347,7 @@ def run_b200(args):
     line.update(extra)
     if world == 1 and not args.skip_cpu_baseline:
         threads = os.cpu_count() or 1
-        sb, ss = (4, 3) if B > 1 else (1, 10)
+        sb, ss = (min(B, 16), 10) if B > 1 else (1, D)
         fps, ms_c, desc = cpu_oracle_rate(cfg, sd, T, D, use_cfg, sb, ss, threads)
         line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": desc,
                                 "ms_per_denoise_step_at_sample_batch": ms_c}

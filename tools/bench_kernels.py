@@ -1,0 +1,111 @@
+#!/usr/bin/env python
+"""Per-kernel timing of the encoder-layer kernels at a bench workload's shapes (CUDA events, warm, looped).
+
+    python tools/bench_kernels.py [--rows 25216] [--seq 197] [--iters 20] [--fmt fp16]
+
+Rotates over several buffer sets larger than L2 in total so that no launch finds its operands L2-resident from
+its own previous launch (weights stay hot, as in the real step).  Prints microseconds per launch and the
+achieved TFLOP/s or GB/s against MEASURED_PEAKS.json.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from gesturediffusion_b200 import kernels as K  # noqa: E402
+
+
+def timed(fn, iters):
+    for i in range(3):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3        # us
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=0)
+    ap.add_argument("--seq", type=int, default=197)
+    ap.add_argument("--nseq", type=int, default=128)
+    ap.add_argument("--iters", type=int, default=24)
+    ap.add_argument("--fmt", default="fp16")
+    ap.add_argument("--sets", type=int, default=3)
+    ap.add_argument("--only", default="")
+    a = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    act = torch.float16 if a.fmt == "fp16" else torch.bfloat16
+    d, F, H = 512, 1024, 4
+    S, nseq = a.seq, a.nseq
+    M = a.rows or S * nseq
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0, "hbm_gbs": 6650.0}
+    g = torch.Generator(device=dev).manual_seed(0)
+
+    def rnd(*shape, dtype=torch.float32, scale=1.0):
+        return (torch.randn(*shape, device=dev, generator=g) * scale).to(dtype)
+
+    ns = a.sets
+    Xa = [rnd(M, d, dtype=act) for _ in range(ns)]
+    X32 = [rnd(M, d) for _ in range(ns)]
+    Y32 = [torch.empty(M, d, device=dev) for _ in range(ns)]
+    QKV = [rnd(M, 3 * d, dtype=act) for _ in range(ns)]
+    ATT = [rnd(M, d, dtype=act) for _ in range(ns)]
+    Hh = [rnd(M, F, dtype=act) for _ in range(ns)]
+    w_qkv, b_qkv = rnd(3 * d, d, dtype=act, scale=0.04), rnd(3 * d)
+    w_o, b_o = rnd(d, d, dtype=act, scale=0.04), rnd(d)
+    w_1, b_1 = rnd(F, d, dtype=act, scale=0.04), rnd(F)
+    w_2, b_2 = rnd(d, F, dtype=act, scale=0.03), rnd(d)
+    gam, bet = rnd(d), rnd(d)
+    out = {}
+
+    def rec(name, us, flops=None, nbytes=None):
+        line = "%-34s %8.1f us" % (name, us)
+        if flops:
+            tf = flops / us / 1e6
+            line += "  %7.1f TFLOP/s (%.2f of burst peak)" % (tf, tf / peaks["bf16_tflops"])
+        if nbytes:
+            gb = nbytes / us / 1e3
+            line += "  %7.1f GB/s algorithmic (%.2f of HBM peak)" % (gb, gb / peaks["hbm_gbs"])
+        print(line)
+        out[name] = us
+
+    esz = 2
+    want = set(a.only.split(",")) if a.only else None
+
+    def on(n):
+        return want is None or n in want
+
+    if on("qkv"):
+        rec("gemm qkv  N=1536 K=512 ->h16", timed(lambda i: K.gemm(Xa[i % ns], w_qkv, K.epilogue(bias=b_qkv, out_h16=QKV[i % ns])), a.iters),
+            flops=2.0 * M * 3 * d * d, nbytes=M * d * esz + M * 3 * d * esz)
+    if on("attn"):
+        rec("attention S=%d H=4 dh=128" % S, timed(lambda i: K.attention(QKV[i % ns], ATT[i % ns], M // S, S, H, d // H), a.iters),
+            flops=4.0 * (M // S) * H * S * S * (d // H), nbytes=M * 4 * d * esz)
+    if on("oproj"):
+        rec("gemm o    N=512 K=512 +res ->f32", timed(lambda i: K.gemm(ATT[i % ns], w_o, K.epilogue(bias=b_o, residual=X32[i % ns], out_f32=Y32[i % ns])), a.iters),
+            flops=2.0 * M * d * d, nbytes=M * d * (esz + 4 + 4))
+    if on("ln"):
+        rec("layernorm d=512 ->f32+h16", timed(lambda i: K.layernorm(Y32[i % ns], gam, bet, out_f32=X32[i % ns], out_h16=Xa[i % ns]), a.iters),
+            nbytes=M * d * (4 + 4 + esz))
+    if on("ffn1"):
+        rec("gemm ffn1 N=1024 K=512 gelu ->h16", timed(lambda i: K.gemm(Xa[i % ns], w_1, K.epilogue(bias=b_1, act=K.GD_ACT_GELU_ERF, out_h16=Hh[i % ns])), a.iters),
+            flops=2.0 * M * F * d, nbytes=M * d * esz + M * F * esz)
+    if on("ffn2"):
+        rec("gemm ffn2 N=512 K=1024 +res ->f32", timed(lambda i: K.gemm(Hh[i % ns], w_2, K.epilogue(bias=b_2, residual=X32[i % ns], out_f32=Y32[i % ns])), a.iters),
+            flops=2.0 * M * d * F, nbytes=M * F * esz + M * d * 8)
+    print(json.dumps({"rows": M, "S": S, "us": out}))
+
+
+if __name__ == "__main__":
+    main()
