@@ -7,6 +7,8 @@
 //    m16n8k16 bf16 tensor-core tiles with fp32 accumulation, online softmax with quad shuffles.
 //    (~5% of the step's flops; S <= a few hundred, so one CTA sees the whole K/V of its head.)
 //  * fp32 path: SIMT reference-precision kernel for "fp32 mode" parity runs.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace gd {
@@ -233,6 +235,18 @@ attention_f32_kernel(const float* __restrict__ qkv, float* __restrict__ out, int
   }
 }
 
+bool attention_tc_supported(int S, int n_heads, int head_dim);
+int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_heads, int fmt, cudaStream_t stream);
+
+static bool attention_legacy_forced() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GD_ATTN_LEGACY");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v == 1;
+}
+
 }  // namespace gd
 
 extern "C" int gd_attention_h16(const void* qkv, void* out, int32_t n_seq, int32_t S, int32_t n_heads,
@@ -246,6 +260,11 @@ extern "C" int gd_attention_h16(const void* qkv, void* out, int32_t n_seq, int32
   const float sl2 = (1.0f / sqrtf((float)head_dim)) * 1.4426950408889634f;
   dim3 grid(ceil_div(S, AT_BQ), n_heads, n_seq);
   cudaStream_t st = (cudaStream_t)stream;
+  // tcgen05/TMEM kernel for the encoder shapes (head_dim 128, S <= 256); the mma.sync flash kernel below
+  // covers other head dims and longer sequences (GD_ATTN_LEGACY=1 forces it, for A/B timing).
+  if (attention_tc_supported(S, n_heads, head_dim) && (((uintptr_t)qkv) & 15) == 0 && (((uintptr_t)out) & 15) == 0 &&
+      !attention_legacy_forced())
+    return launch_attention_tc(qkv, out, n_seq, S, n_heads, fmt, st);
   const __nv_bfloat16* q = (const __nv_bfloat16*)qkv;
   __nv_bfloat16* o = (__nv_bfloat16*)out;
 #define GD_ATH(DHV)                                                                              \

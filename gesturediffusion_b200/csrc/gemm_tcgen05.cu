@@ -267,7 +267,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2D bf16 row-major [rows, cols] with row stride ld elements; box = [box_rows, 64 cols], SW128.
-static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt) {
+int make_tmap_2d(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
@@ -288,6 +288,15 @@ static int make_tmap(CUtensorMap* out, const void* base, int rows, int cols, int
 }
 
 static int g_num_sms = 0;
+
+int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+  }
+  return g_num_sms;
+}
 
 // Which compile-time epilogue serves this gdEpilogue (EPI_GENERIC handles everything).
 static int pick_epilogue(const gdEpilogue* ep, int N) {
@@ -317,9 +326,9 @@ static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, in
     attr_set = true;
   }
   CUtensorMap ta, tw;
-  int rc = make_tmap(&ta, A, M, K, lda, kBM, fmt);
+  int rc = make_tmap_2d(&ta, A, M, K, lda, kBM, fmt);
   if (rc) return rc;
-  rc = make_tmap(&tw, W, N, K, ldw, BN, fmt);
+  rc = make_tmap_2d(&tw, W, N, K, ldw, BN, fmt);
   if (rc) return rc;
   const int tiles = ceil_div(M, kBM) * ceil_div(N, BN);
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;

@@ -6,6 +6,12 @@
 #include <stdint.h>
 
 namespace gd {
+
+// host helpers defined in gemm_tcgen05.cu
+// 2D 16-bit row-major tensor [rows, cols] with row stride ld elements; box = [box_rows, 64 cols], 128B swizzle.
+int make_tmap_2d(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt);
+int num_sms();
+
 namespace ptx {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

@@ -110,7 +110,11 @@ def test_gemm_epilogue_rowmap_dup_tables_transposed(cuda_device, dtype):
 
 # ------------------------------------------------------------------ attention / LN
 @pytest.mark.parametrize("n_seq,S,H,dh", [(3, 21, 4, 32), (2, 121, 4, 128), (2, 197, 4, 128), (1, 64, 2, 64),
-                                         (2, 301, 4, 128)])
+                                         (2, 301, 4, 128),
+                                         # tcgen05 kernel (dh 128, S <= 256): edge lengths, one and two query tiles,
+                                         # and enough (sequence, head) items for several units per CTA
+                                         (1, 1, 1, 128), (3, 16, 2, 128), (2, 128, 4, 128), (2, 129, 4, 128),
+                                         (1, 256, 4, 128), (5, 61, 3, 128), (160, 121, 4, 128), (100, 197, 4, 128)])
 @pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
 def test_attention(cuda_device, n_seq, S, H, dh, dtype):
     Kn = _K()
