@@ -1,0 +1,349 @@
+// gemm_ln.cu -- 16-bit tcgen05 GEMM with bias + residual + LayerNorm fused into the epilogue:
+//   X = LayerNorm(residual + A @ W^T + bias) * gamma + beta        (post-norm sub-layer tail of
+//   nn.TransformerEncoderLayer: out_proj + norm1 and linear2 + norm2, mdm.py:90-96)
+// written as fp32 (the residual stream) and as the 16-bit operand of the next GEMM, so the pre-norm sum
+// never goes to HBM (saves one fp32 write + one fp32 read of the whole activation per sub-layer and the
+// separate LayerNorm launch).
+//
+// A LayerNorm row spans the full N = d columns; one CTA's TMEM holds two 128 x BN fp32 accumulators (double
+// buffered), so a row is split over the TWO CTAs of a thread-block cluster (N = 2*BN, CTA rank r owns columns
+// [r*BN, (r+1)*BN)).  Per 128-row tile each epilogue thread owns one row x BN/2 columns:
+//   pass A  y = acc + bias + residual (residual fetched row-contiguously one block ahead and transposed
+//           through swizzled smem), running (mean, M2) by Chan's update, y written back to TMEM in place;
+//   exchange  the four partial (mean, M2) of a row -- 2 column halves x 2 CTAs -- are written to both CTAs'
+//           shared memory (st.shared::cluster) and published with one cluster-scope mbarrier per tile parity;
+//   pass B  z = (y - mean) * rstd * gamma + beta from TMEM, transposed through smem, row-contiguous stores.
+// Statistics are two-pass quality (no E[x^2] - mean^2 cancellation).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace gd {
+
+constexpr int kLnBM = 128, kLnBK = 64, kLnEpiWarps = 8, kLnThreads = 320, kLnStages = 3;
+
+template <int BN>
+struct LnCfg {
+  static constexpr int kABytes = kLnBM * kLnBK * 2;
+  static constexpr int kBBytes = BN * kLnBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagingBytes = kLnEpiWarps * 4096;
+  static constexpr int kVecBytes = 3 * BN * 4;                  // bias, gamma, beta slices of this CTA
+  static constexpr int kStatBytes = 2 * 4 * kLnBM * 8;          // [parity][part][row] (mean, M2)
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kLnStages * kStageBytes + kStagingBytes + kVecBytes + kStatBytes + kBarBytes + 1024;
+  static constexpr int kTmemCols = 2 * BN;
+};
+
+struct LnParams {
+  const float* bias; const float* gamma; const float* beta;
+  const float* residual; int ld_res;
+  float* out_f32; int ld_out;
+  void* out_h16; int ld_out_h16; int h16_fmt;
+  float eps;
+  int M, K;
+  uint32_t idesc;
+};
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
+gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                       const LnParams p) {
+  using Cfg = LnCfg<BN>;
+  constexpr int N = 2 * BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + kLnStages * Cfg::kStageBytes;
+  float* vecs = reinterpret_cast<float*>(staging + Cfg::kStagingBytes);          // bias | gamma | beta
+  uint8_t* stats = reinterpret_cast<uint8_t*>(vecs) + Cfg::kVecBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stats + Cfg::kStatBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = full_bar + kLnStages;
+  uint64_t* tfull_bar = empty_bar + kLnStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint64_t* stat_bar = tempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int n_clusters = (int)gridDim.x >> 1, cluster_id = (int)blockIdx.x >> 1;
+  const int M = p.M;
+  const int m_tiles = (M + kLnBM - 1) / kLnBM;
+  const int k_blocks = (p.K + kLnBK - 1) / kLnBK;
+  const int n_cta = (int)rank * BN;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_a);
+    ptx::prefetch_tensormap(&tmap_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kLnStages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(&tfull_bar[b], 1);
+      ptx::mbar_init(&tempty_bar[b], kLnEpiWarps);
+      ptx::mbar_init(&stat_bar[b], 2 * kLnEpiWarps);       // 8 local + 8 peer warps
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  for (int i = threadIdx.x; i < BN; i += kLnThreads) {
+    vecs[i] = p.bias[n_cta + i];
+    vecs[BN + i] = p.gamma[n_cta + i];
+    vecs[2 * BN + i] = p.beta[n_cta + i];
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();                                   // peer's barriers are initialised before any remote arrive
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters) {
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kLnBK, m_blk * kLnBM);
+          ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kLnBK, n_cta);
+          if (++stage == kLnStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ UMMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
+        const int buf = local & 1;
+        const uint32_t use = (uint32_t)(local >> 1);
+        ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < kLnBK / 16; ++k) {
+            const uint64_t da = ptx::umma_desc_k_sw128(sa + k * 32);
+            const uint64_t db = ptx::umma_desc_k_sw128(sb + k * 32);
+            ptx::umma_h16(tmem_d, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);
+          if (++stage == kLnStages) { stage = 0; phase ^= 1; }
+        }
+        ptx::umma_commit(&tfull_bar[buf]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps
+    const int ew = warp - 2;
+    const int quarter = warp & 3;
+    const int half = ew >> 2;
+    constexpr int CW = BN / 2;                               // columns per warp
+    constexpr int NCH = CW / 32;
+    const uint32_t stg = ptx::smem_u32(staging) + (uint32_t)ew * 4096;
+    const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;      // this warp's bias slice
+    const uint32_t stats_s = ptx::smem_u32(stats);
+    const uint32_t stats_peer = ptx::mapa(stats_s, rank ^ 1u);
+    const uint32_t part = rank * 2u + (uint32_t)half;
+    const int c4 = lane & 7, rsub = lane >> 3;
+    const int row_in_tile = quarter * 32 + lane;
+    int local = 0;
+    for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
+      const int buf = local & 1;
+      const uint32_t use = (uint32_t)(local >> 1);
+      const int m_warp = m_blk * kLnBM + quarter * 32;
+      const int n_warp = n_cta + half * CW;
+      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * CW);
+      // residual block (row-contiguous: lane -> row it*4 + lane/8, 4 columns at 4*(lane%8)), one block ahead
+      float4 pre[8];
+      auto fetch = [&](int n0) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int mm = m_warp + it * 4 + rsub;
+          pre[it] = (mm < M) ? *reinterpret_cast<const float4*>(p.residual + (size_t)mm * p.ld_res + n0 + c4 * 4)
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      };
+      fetch(n_warp);
+      ptx::mbar_wait(&tfull_bar[buf], use & 1);
+      ptx::tc_fence_after();
+
+      // ---- pass A: y = acc + bias + residual -> TMEM, running row statistics
+      float r_mean = 0.f, r_m2 = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        float v[32];
+        ptx::tmem_ld_32x32(taddr0 + c * 32, v);
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int rl = it * 4 + rsub;
+          ptx::sts_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4), pre[it].x, pre[it].y, pre[it].z, pre[it].w);
+        }
+        __syncwarp();
+        if (c + 1 < NCH) fetch(n_warp + (c + 1) * 32);
+        float cs = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 r = ptx::lds_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4));
+          const float4 b = ptx::lds_v4(vec_s + (c * 32 + j * 4) * 4);
+          v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y; v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
+          cs += (v[4 * j] + v[4 * j + 1]) + (v[4 * j + 2] + v[4 * j + 3]);
+        }
+        const float cm = cs * (1.0f / 32.0f);
+        float cq = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) cq = fmaf(v[j] - cm, v[j] - cm, cq);
+        // Chan: combine (c*32, r_mean, r_m2) with (32, cm, cq)
+        const float na = (float)(c * 32), nb = 32.f, nt = na + nb;
+        const float delta = cm - r_mean;
+        r_mean += delta * (nb / nt);
+        r_m2 += cq + delta * delta * (na * nb / nt);
+        ptx::tmem_st_32x32(taddr0 + c * 32, v);
+        __syncwarp();
+      }
+      ptx::tmem_st_wait();
+
+      // ---- exchange the partial statistics of this row with the other column half and the peer CTA
+      const uint32_t par = (uint32_t)(local & 1);
+      const uint32_t off = ((par * 4u + part) * kLnBM + (uint32_t)row_in_tile) * 8u;
+      asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(stats_s + off), "f"(r_mean), "f"(r_m2) : "memory");
+      ptx::st_cluster_v2(stats_peer + off, r_mean, r_m2);
+      __syncwarp();
+      if (lane == 0) {
+        const uint32_t bar_local = ptx::smem_u32(&stat_bar[par]);
+        ptx::mbar_arrive_cluster(ptx::mapa(bar_local, rank));
+        ptx::mbar_arrive_cluster(ptx::mapa(bar_local, rank ^ 1u));
+      }
+      ptx::mbar_wait_cluster(&stat_bar[par], use & 1);
+      float mean = 0.f, m2 = 0.f;
+      {
+        float pm[4], pq[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t a = stats_s + ((par * 4u + (uint32_t)q) * kLnBM + (uint32_t)row_in_tile) * 8u;
+          asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(pm[q]), "=f"(pq[q]) : "r"(a) : "memory");
+          mean += pm[q];
+        }
+        mean *= 0.25f;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) m2 += pq[q] + (float)CW * (pm[q] - mean) * (pm[q] - mean);
+      }
+      const float rstd = rsqrtf(m2 * (1.0f / (float)N) + p.eps);
+
+      // ---- pass B: normalise from TMEM, transpose through smem, row-contiguous stores
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        float v[32];
+        ptx::tmem_ld_32x32(taddr0 + c * 32, v);
+        if (c == NCH - 1) {                                  // accumulator buffer fully consumed
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty_bar[buf]);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 g = ptx::lds_v4(vec_s + (BN + c * 32 + j * 4) * 4);
+          const float4 b = ptx::lds_v4(vec_s + (2 * BN + c * 32 + j * 4) * 4);
+          ptx::sts_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4),
+                      (v[4 * j] - mean) * rstd * g.x + b.x, (v[4 * j + 1] - mean) * rstd * g.y + b.y,
+                      (v[4 * j + 2] - mean) * rstd * g.z + b.z, (v[4 * j + 3] - mean) * rstd * g.w + b.w);
+        }
+        __syncwarp();
+        const int n = n_warp + c * 32 + c4 * 4;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int rl = it * 4 + rsub, mm = m_warp + rl;
+          const float4 w = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
+          if (mm < M) {
+            if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + (size_t)mm * p.ld_out + n) = w;
+            if (p.out_h16) {
+              uint2 pk;
+              pk.x = pack_h16x2(w.x, w.y, p.h16_fmt);
+              pk.y = pack_h16x2(w.z, w.w, p.h16_fmt);
+              *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(p.out_h16) + (size_t)mm * p.ld_out_h16 + n) = pk;
+            }
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();                                   // no CTA exits while its peer may still write its smem
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+template <int BN>
+static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p,
+                          cudaStream_t stream) {
+  using Cfg = LnCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  CUtensorMap ta, tw;
+  int rc = make_tmap_2d(&ta, A, p.M, p.K, lda, kLnBM, fmt);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tw, W, 2 * BN, p.K, ldw, BN, fmt);
+  if (rc) return rc;
+  const int sms = num_sms();
+  GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
+  const int m_tiles = ceil_div(p.M, kLnBM);
+  const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
+  gemm_ln_tcgen05_kernel<BN><<<2 * clusters, kLnThreads, Cfg::kSmemBytes, stream>>>(ta, tw, p);
+  GD_LAUNCH_CHECK();
+  return GD_OK;
+}
+
+}  // namespace gd
+
+extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                              int32_t fmt, const float* bias, const float* residual, int32_t ld_res,
+                              const float* gamma, const float* beta, float eps, float* out_f32, int32_t ld_out,
+                              void* out_h16, int32_t ld_out_h16, int32_t h16_fmt, void* stream) {
+  using namespace gd;
+  GD_REQUIRE(A && W && bias && residual && gamma && beta && (out_f32 || out_h16), "gd_gemm_h16_ln: null pointer");
+  GD_REQUIRE(M > 0 && K > 0, "gd_gemm_h16_ln: bad shape M=%d K=%d", M, K);
+  if (N != 256 && N != 512) {
+    set_error("gd_gemm_h16_ln: N=%d not in {256, 512} (use gd_gemm_h16 + gd_layernorm)", N);
+    return GD_ERR_UNSUPPORTED;
+  }
+  GD_REQUIRE(fmt == GD_BF16 || fmt == GD_FP16, "gd_gemm_h16_ln: fmt must be GD_BF16 or GD_FP16");
+  GD_REQUIRE(!out_h16 || h16_fmt == GD_BF16 || h16_fmt == GD_FP16, "gd_gemm_h16_ln: bad h16_fmt");
+  GD_REQUIRE(lda % 8 == 0 && ldw % 8 == 0 && lda >= K && ldw >= K,
+             "gd_gemm_h16_ln: lda/ldw must be multiples of 8 and >= K (lda=%d ldw=%d K=%d)", lda, ldw, K);
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  GD_REQUIRE(al16(A) && al16(W) && al16(residual) && (!out_f32 || al16(out_f32)) && (!out_h16 || al16(out_h16)),
+             "gd_gemm_h16_ln: operands must be 16-byte aligned");
+  GD_REQUIRE(ld_res >= N && ld_res % 4 == 0 && (!out_f32 || (ld_out >= N && ld_out % 4 == 0)) &&
+                 (!out_h16 || (ld_out_h16 >= N && ld_out_h16 % 4 == 0)),
+             "gd_gemm_h16_ln: leading dimensions must be >= N and multiples of 4");
+  LnParams p;
+  p.bias = bias; p.gamma = gamma; p.beta = beta;
+  p.residual = residual; p.ld_res = ld_res;
+  p.out_f32 = out_f32; p.ld_out = ld_out;
+  p.out_h16 = out_h16; p.ld_out_h16 = ld_out_h16; p.h16_fmt = h16_fmt;
+  p.eps = eps; p.M = M; p.K = K;
+  p.idesc = ptx::umma_idesc_h16_f32(kLnBM, N / 2, fmt == GD_FP16);
+  if (N == 512) return launch_gemm_ln<256>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
+  return launch_gemm_ln<128>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
+}

@@ -99,6 +99,7 @@ class DenoiserEngine:
         if self.d // self.H not in (32, 64, 128):
             raise ValueError("latent_dim/num_heads must be 32, 64 or 128")
         self._ws = {}
+        self.fuse_ln = True            # GEMM + residual + LayerNorm in one kernel where gd_gemm_h16_ln supports d
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -291,10 +292,20 @@ class DenoiserEngine:
             rc, rs = self.rope_tables(T)
             K.local_attention(ws["XL"], rc, rs, X32, xa_b, nb * B, T, d, self.cl_head, 10)
         dh = d // self.H
+        fused_ln = self.fuse_ln and self.h16 and d in (256, 512)
         for l in range(self.L):
             p = "l%d." % l
             K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(ws["QKV"])), K=d)
             K.attention(ws["QKV"], ws["ATT"], nb * B, S, self.H, dh)
+            if fused_ln:
+                # out_proj + residual + norm1 and linear2 + residual + norm2, each in ONE kernel (2-CTA cluster
+                # LayerNorm epilogue); the residual stream X32 is updated in place
+                K.gemm_ln(ws["ATT"], w[p + "o.w"], w[p + "o.b"], X32, w[p + "norm1.g"], w[p + "norm1.b"],
+                          out_f32=X32, out_h16=xa_b, K=d)
+                K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
+                K.gemm_ln(ws["Hh"], w[p + "f2.w"], w[p + "f2.b"], X32, w[p + "norm2.g"], w[p + "norm2.b"],
+                          out_f32=X32, out_h16=xa_b, K=self.F)
+                continue
             K.gemm(ws["ATT"], w[p + "o.w"], K.epilogue(bias=w[p + "o.b"], residual=X32, out_f32=ws["Y32"]), K=d)
             K.layernorm(ws["Y32"], w[p + "norm1.g"], w[p + "norm1.b"], out_f32=X32, out_h16=xa_b)
             K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
@@ -304,7 +315,8 @@ class DenoiserEngine:
         K.gemm(Xa, w["out.w"], K.epilogue(bias=w["out.b"], out_t=ws["OUT"], t_s=S, t_t=T, t_skip=1), K=d)
 
     def kernels_per_step(self):
-        return 2 + (1 if self.arch == "v2" else 0) + 7 * self.L + 1
+        per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512)) else 7
+        return 2 + (1 if self.arch == "v2" else 0) + per_layer * self.L + 1
 
     def flops_per_step(self, B, T, nb):
         """Algorithmic flops of one denoiser evaluation (BASELINE.md section 5 formula)."""

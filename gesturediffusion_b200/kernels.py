@@ -109,6 +109,28 @@ def gemm(a, w, ep, M=None, N=None, K=None):
         _cabi.check(rc, "gd_gemm_f32")
 
 
+def gemm_ln_supported(a, N):
+    """gd_gemm_h16_ln covers 16-bit operands and N in {256, 512}."""
+    return a.dtype in H16 and N in (256, 512)
+
+
+def gemm_ln(a, w, bias, residual, gamma, beta, out_f32=None, out_h16=None, eps=1e-5, K=None):
+    """LayerNorm(residual + a @ w^T + bias) * gamma + beta in one kernel (tcgen05 GEMM, 2-CTA cluster epilogue)."""
+    lib = _cabi.load()
+    M, N = a.shape[0], w.shape[0]
+    K = a.shape[1] if K is None else K
+    with _Timed("gemm_ln_h16", M=M, N=N, K=K):
+        rc = lib.gd_gemm_h16_ln(_dev(a, a.dtype, "A"), a.stride(0), _dev(w, a.dtype, "W"), w.stride(0), M, N, K,
+                                fmt_of(a), _dev(bias, torch.float32, "bias"),
+                                _dev(residual, torch.float32, "residual"), residual.stride(0),
+                                _dev(gamma, torch.float32, "gamma"), _dev(beta, torch.float32, "beta"), eps,
+                                _dev(out_f32, torch.float32, "out_f32"),
+                                out_f32.stride(0) if out_f32 is not None else 0,
+                                _dev(out_h16, "h16", "out_h16"), out_h16.stride(0) if out_h16 is not None else 0,
+                                fmt_of(out_h16), _cabi.stream_handle())
+    _cabi.check(rc, "gd_gemm_h16_ln")
+
+
 def attention(qkv, out, n_seq, S, n_heads, head_dim):
     lib = _cabi.load()
     with _Timed("attention", n_seq=n_seq, S=S, H=n_heads, dh=head_dim):

@@ -82,6 +82,18 @@ int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ldw,
 int gd_gemm_f32(const float* A, int32_t lda, const float* W, int32_t ldw,
                 int32_t M, int32_t N, int32_t K, const gdEpilogue* ep, void* stream);
 
+/* Post-norm sub-layer tail in one kernel (out_proj + residual + norm1, linear2 + residual + norm2 of
+ * nn.TransformerEncoderLayer, mdm.py:90-96; norm_first=False, eps 1e-5):
+ *   X = LayerNorm(residual + A[M,K] @ W[N,K]^T + bias) * gamma + beta
+ * out_f32 [M, ld_out] and / or out_h16 [M, ld_out_h16] (h16_fmt).  N must be 256 or 512 (= 2 x the per-CTA
+ * accumulator width: a row is normalised across the two CTAs of a thread-block cluster through distributed
+ * shared memory); other widths return GD_ERR_UNSUPPORTED and callers use gd_gemm_h16 + gd_layernorm.
+ * residual may alias out_f32 (each element is read before it is written, by the same thread). */
+int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                   int32_t fmt, const float* bias, const float* residual, int32_t ld_res,
+                   const float* gamma, const float* beta, float eps, float* out_f32, int32_t ld_out,
+                   void* out_h16, int32_t ld_out_h16, int32_t h16_fmt, void* stream);
+
 /* Full softmax self-attention of nn.MultiheadAttention inside nn.TransformerEncoderLayer
  * (mdm.py:90-96,216; no mask, scale 1/sqrt(head_dim)).  qkv is the packed in_proj output
  * [n_seq*S, 3*d] (q | k | v, heads contiguous inside each); out is [n_seq*S, d]. */

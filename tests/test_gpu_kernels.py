@@ -148,6 +148,45 @@ def test_layernorm(cuda_device, rows, d):
         assert torch.equal(ob, o32.to(hdt))
 
 
+@pytest.mark.parametrize("M,N,K", [(1, 512, 512), (127, 512, 512), (129, 256, 64), (1000, 512, 1024),
+                                   (128 * 150 + 77, 512, 512), (4100, 256, 512)])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16"])
+def test_gemm_ln_fused(cuda_device, M, N, K, dtype):
+    """gd_gemm_h16_ln == LayerNorm(residual + A W^T + bias) (float64 reference on the rounded operands), in place on
+    the residual stream; covers single / partial tiles, several tiles per cluster and both cluster widths."""
+    Kn = _K()
+    tdt = TDT[dtype]
+    g = torch.Generator(device="cuda").manual_seed(M + N)
+    a = torch.randn(M, K, device="cuda", generator=g).to(tdt)
+    w = (torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K)).to(tdt)
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g) * 2 + 0.5
+    gamma = 1 + 0.1 * torch.randn(N, device="cuda", generator=g)
+    beta = 0.1 * torch.randn(N, device="cuda", generator=g)
+    y = res.double() + a.double() @ w.double().t() + bias.double()
+    ref = torch.nn.functional.layer_norm(y, (N,), gamma.double(), beta.double(), 1e-5)
+    x32 = res.clone()
+    xh = torch.zeros(M, N, device="cuda", dtype=tdt)
+    Kn.gemm_ln(a, w, bias, x32, gamma, beta, out_f32=x32, out_h16=xh)
+    assert rel_l2(x32, ref) < 5e-6
+    assert torch.equal(xh, x32.to(tdt))
+    # separate outputs, residual untouched
+    o32 = torch.empty_like(res)
+    Kn.gemm_ln(a, w, bias, res, gamma, beta, out_f32=o32)
+    assert torch.equal(o32, x32)
+
+
+def test_gemm_ln_rejects_other_widths(cuda_device):
+    from gesturediffusion_b200 import _cabi
+    Kn = _K()
+    a = torch.zeros(8, 64, device="cuda", dtype=torch.float16)
+    w = torch.zeros(384, 64, device="cuda", dtype=torch.float16)
+    v = torch.zeros(384, device="cuda")
+    r = torch.zeros(8, 384, device="cuda")
+    with pytest.raises(_cabi.GdError, match="not in"):
+        Kn.gemm_ln(a, w, v, r, v, v, out_f32=r)
+
+
 # ------------------------------------------------------------------ local attention + RoPE
 @pytest.mark.parametrize("n_seq,T,d,heads", [(3, 20, 128, 8), (2, 120, 512, 8), (1, 600, 512, 8), (2, 10, 128, 8)])
 def test_local_attention_rope(cuda_device, n_seq, T, d, heads):

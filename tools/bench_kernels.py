@@ -104,6 +104,12 @@ def main():
     if on("ffn2"):
         rec("gemm ffn2 N=512 K=1024 +res ->f32", timed(lambda i: K.gemm(Hh[i % ns], w_2, K.epilogue(bias=b_2, residual=X32[i % ns], out_f32=Y32[i % ns])), a.iters),
             flops=2.0 * M * d * F, nbytes=M * F * esz + M * d * 8)
+    if on("oln"):
+        rec("gemm o+LN   N=512 K=512 ->f32+h16", timed(lambda i: K.gemm_ln(ATT[i % ns], w_o, b_o, X32[i % ns], gam, bet, out_f32=X32[i % ns], out_h16=Xa[i % ns]), a.iters),
+            flops=2.0 * M * d * d, nbytes=M * d * (esz + 4 + 4 + esz))
+    if on("f2ln"):
+        rec("gemm ffn2+LN N=512 K=1024 ->f32+h16", timed(lambda i: K.gemm_ln(Hh[i % ns], w_2, b_2, X32[i % ns], gam, bet, out_f32=X32[i % ns], out_h16=Xa[i % ns]), a.iters),
+            flops=2.0 * M * d * F, nbytes=M * F * esz + M * d * (4 + 4 + esz))
     print(json.dumps({"rows": M, "S": S, "us": out}))
 
 
