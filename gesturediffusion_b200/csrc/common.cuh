@@ -64,11 +64,10 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // 16-bit packing in the runtime-selected format (GD_BF16 / GD_FP16); fp16 saturates instead of
 // overflowing to inf.
 __device__ __forceinline__ uint32_t pack_h16x2(float lo, float hi, int fmt) {
+  uint32_t r;
   if (fmt == GD_FP16) {
-    lo = fminf(fmaxf(lo, -65504.f), 65504.f);
-    hi = fminf(fmaxf(hi, -65504.f), 65504.f);
-    __half2 p = __floats2half2_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&p);
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));   // one F2FP, clamps to +-65504
+    return r;
   }
   return pack_bf16x2(lo, hi);
 }
@@ -80,6 +79,26 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }
 __device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+
+// erf-GELU without erff(): erfc(z) = 2^q(z) on z = |x|/sqrt(2) in [0, 4.2] with q a degree-7 polynomial
+// through q(0) = 0 (weighted minimax fit of log2 erfc, |erf error| < 8e-8 in exact arithmetic), so
+//   gelu(x) = max(x, 0) - |0.5 x 2^q|
+// which has no cancellation in the negative tail.  13 FMA/ALU-pipe instructions + one MUFU.EX2 instead of
+// ~25 for the erff() form; measured against float64 erf-GELU over [-8, 8]: max abs error 6.2e-7 (torch's own
+// fp32 gelu: 1.2e-6).  Used by the 16-bit tensor-core epilogue (outputs are rounded to 16 bit afterwards).
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float z = fminf(fabsf(x) * 0.70710678118654752440f, 4.2f);
+  float p = 1.002210425e-04f;
+  p = fmaf(p, z, -4.615735962e-04f);
+  p = fmaf(p, z, -2.302234498e-03f);
+  p = fmaf(p, z, 2.945250839e-02f);
+  p = fmaf(p, z, -1.489636641e-01f);
+  p = fmaf(p, z, -9.183286457e-01f);
+  p = fmaf(p, z, -1.627913732e+00f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(p * z));
+  return fmaxf(x, 0.f) - fabsf((0.5f * x) * e);
+}
 
 // ------------------------------------------------------------------ fused GEMM epilogue
 // Processes CH consecutive columns [n0, n0+CH) of logical row m.  See gdEpilogue in gd_b200.h.

@@ -79,8 +79,8 @@ __device__ __forceinline__ void epi_block(const gdEpilogue& ep, uint32_t stg, in
       f4_add(w0, b0);
       f4_add(w1, b1);
       if constexpr (EPI == EPI_BIAS_GELU_H16) {
-        w0.x = gelu_erf(w0.x); w0.y = gelu_erf(w0.y); w0.z = gelu_erf(w0.z); w0.w = gelu_erf(w0.w);
-        w1.x = gelu_erf(w1.x); w1.y = gelu_erf(w1.y); w1.z = gelu_erf(w1.z); w1.w = gelu_erf(w1.w);
+        w0.x = gelu_fast(w0.x); w0.y = gelu_fast(w0.y); w0.z = gelu_fast(w0.z); w0.w = gelu_fast(w0.w);
+        w1.x = gelu_fast(w1.x); w1.y = gelu_fast(w1.y); w1.z = gelu_fast(w1.z); w1.w = gelu_fast(w1.w);
       }
       uint4 q;
       q.x = pack_h16x2(w0.x, w0.y, ep.h16_fmt);

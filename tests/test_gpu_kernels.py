@@ -50,6 +50,37 @@ def test_gemm_bias(cuda_device, M, N, K, dtype):
     assert rel_l2(out, ref) < (2e-6 if dtype == "fp32" else 1e-5)     # fp32 accumulation in both
 
 
+@pytest.mark.parametrize("M,N,K", [(700, 1024, 512), (129, 512, 64), (25216, 1024, 512)])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16"])
+def test_gemm_specialised_epilogues(cuda_device, M, N, K, dtype):
+    """The three compile-time epilogues of the tcgen05 GEMM (bias->16 bit, bias+erf-GELU->16 bit with the
+    polynomial erfc form, bias+residual->fp32) against float64; the GELU path must agree with the exact erf
+    form to within one 16-bit rounding of the output, i.e. its own error (6e-7 abs) is invisible."""
+    Kn = _K()
+    tdt = TDT[dtype]
+    g = torch.Generator(device="cuda").manual_seed(M + K)
+    a = (torch.randn(M, K, device="cuda", generator=g) * 1.5).to(tdt)
+    w = (torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K)).to(tdt)
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    base = a.double() @ w.double().T + bias.double()
+    oh = torch.empty(M, N, device="cuda", dtype=tdt)
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, out_h16=oh))
+    assert rel_l2(oh.float(), base) < H16_ROUND[dtype]
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, act=Kn.GD_ACT_GELU_ERF, out_h16=oh))
+    ref = _gelu(base)
+    assert rel_l2(oh.float(), ref) < H16_ROUND[dtype]
+    # versus the correctly rounded exact value: never more than one 16-bit ulp away, and almost always equal
+    exact = ref.to(torch.float32).to(tdt)
+    ulp = exact.float().abs() * (2.0 ** -10 if dtype == "fp16" else 2.0 ** -7)
+    diff = (oh.float() - exact.float()).abs()
+    assert bool((diff <= 1.01 * ulp + 3e-6).all())        # 3e-6: fp32 accumulation order + the 6e-7 erfc fit
+    assert float((diff > 0).float().mean()) < 0.05      # rounding flips from the fp32 accumulation order (measured 2 %)
+    o32 = torch.empty(M, N, device="cuda")
+    Kn.gemm(a, w, Kn.epilogue(bias=bias, residual=res, out_f32=o32))
+    assert rel_l2(o32, base + res.double()) < 1e-5
+
+
 @pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
 def test_gemm_epilogue_residual_gelu_h16out(cuda_device, dtype):
     Kn = _K()
