@@ -14,23 +14,25 @@
 //           shared memory (st.shared::cluster) and published with one cluster-scope mbarrier per tile parity;
 //   pass B  z = (y - mean) * rstd * gamma + beta from TMEM, transposed through smem, row-contiguous stores.
 // Statistics are two-pass quality (no E[x^2] - mean^2 cancellation).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
 namespace gd {
 
-constexpr int kLnBM = 128, kLnBK = 64, kLnEpiWarps = 8, kLnThreads = 320, kLnStages = 3;
+constexpr int kLnBM = 128, kLnBK = 64, kLnEpiWarps = 8, kLnThreads = 320, kLnStages = 2;
 
 template <int BN>
 struct LnCfg {
   static constexpr int kABytes = kLnBM * kLnBK * 2;
   static constexpr int kBBytes = BN * kLnBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagingBytes = kLnEpiWarps * 4096;
+  static constexpr int kRingBytes = kLnEpiWarps * 3 * 4096;     // per warp: 2 residual blocks in flight + 1 staging block
   static constexpr int kVecBytes = 3 * BN * 4;                  // bias, gamma, beta slices of this CTA
   static constexpr int kStatBytes = 2 * 4 * kLnBM * 8;          // [parity][part][row] (mean, M2)
-  static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = kLnStages * kStageBytes + kStagingBytes + kVecBytes + kStatBytes + kBarBytes + 1024;
+  static constexpr int kBarBytes = 512;
+  static constexpr int kSmemBytes = kLnStages * kStageBytes + kRingBytes + kVecBytes + kStatBytes + kBarBytes;
   static constexpr int kTmemCols = 2 * BN;
 };
 
@@ -42,18 +44,19 @@ struct LnParams {
   float eps;
   int M, K;
   uint32_t idesc;
+  int dbg;     // GD_LN_DBG diagnostics (results wrong): 1 no statistics exchange, 2 no global stores, 4 no residual, 8 no epilogue
 };
 
 template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
 gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                       const LnParams p) {
+                       const __grid_constant__ CUtensorMap tmap_res, const LnParams p) {
   using Cfg = LnCfg<BN>;
   constexpr int N = 2 * BN;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* staging = smem + kLnStages * Cfg::kStageBytes;
-  float* vecs = reinterpret_cast<float*>(staging + Cfg::kStagingBytes);          // bias | gamma | beta
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* ring = smem + kLnStages * Cfg::kStageBytes;
+  float* vecs = reinterpret_cast<float*>(ring + Cfg::kRingBytes);                // bias | gamma | beta
   uint8_t* stats = reinterpret_cast<uint8_t*>(vecs) + Cfg::kVecBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(stats + Cfg::kStatBytes);
   uint64_t* full_bar = bars;
@@ -61,7 +64,8 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   uint64_t* tfull_bar = empty_bar + kLnStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* stat_bar = tempty_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
+  uint64_t* res_bar = stat_bar + 2;                          // [epilogue warp][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 2 * kLnEpiWarps);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
@@ -74,8 +78,10 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_w);
+    ptx::prefetch_tensormap(&tmap_res);
   }
   if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2 * kLnEpiWarps; ++i) ptx::mbar_init(&res_bar[i], 1);
     for (int s = 0; s < kLnStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
       ptx::mbar_init(&empty_bar[s], 1);
@@ -152,55 +158,82 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     const int half = ew >> 2;
     constexpr int CW = BN / 2;                               // columns per warp
     constexpr int NCH = CW / 32;
-    const uint32_t stg = ptx::smem_u32(staging) + (uint32_t)ew * 4096;
+    // per-warp ring: blocks 0/1 receive the residual ([32 rows x 32 fp32] TMA boxes, 128B swizzle: 16-byte chunk
+    // (c/4) ^ (r&7) of row r -- the layout of the staging block), two blocks in flight ahead of the consumer and
+    // across tile boundaries; block 2 is the staging block of pass B.
+    const uint32_t rbuf = ptx::smem_u32(ring) + (uint32_t)ew * (3 * 4096);
+    const uint32_t stg = rbuf + 2 * 4096;
+    const uint32_t rbar = ptx::smem_u32(&res_bar[2 * ew]);
     const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;      // this warp's bias slice
     const uint32_t stats_s = ptx::smem_u32(stats);
     const uint32_t stats_peer = ptx::mapa(stats_s, rank ^ 1u);
     const uint32_t part = rank * 2u + (uint32_t)half;
     const int c4 = lane & 7, rsub = lane >> 3;
     const int row_in_tile = quarter * 32 + lane;
+    const int n_warp = n_cta + half * CW;
+    const int my_tiles = (m_tiles - cluster_id + n_clusters - 1) / n_clusters;
+    const int total_blocks = my_tiles * NCH;
+    auto issue_residual = [&](int g) {                       // lane 0: residual block g of this warp's sequence
+      const int tl = g / NCH, c = g - tl * NCH;
+      const uint32_t bar = rbar + (uint32_t)(g & 1) * 8;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(4096) : "memory");
+      ptx::tma_load_2d_s(rbuf + (uint32_t)(g & 1) * 4096, &tmap_res, bar, n_warp + c * 32,
+                         (cluster_id + tl * n_clusters) * kLnBM + quarter * 32);
+    };
+    if (lane == 0 && !(p.dbg & 12)) {
+      if (total_blocks > 0) issue_residual(0);
+      if (total_blocks > 1) issue_residual(1);
+    }
     int local = 0;
     for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
       const int m_warp = m_blk * kLnBM + quarter * 32;
-      const int n_warp = n_cta + half * CW;
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * CW);
-      // residual block (row-contiguous: lane -> row it*4 + lane/8, 4 columns at 4*(lane%8)), one block ahead
-      float4 pre[8];
-      auto fetch = [&](int n0) {
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          const int mm = m_warp + it * 4 + rsub;
-          pre[it] = (mm < M) ? *reinterpret_cast<const float4*>(p.residual + (size_t)mm * p.ld_res + n0 + c4 * 4)
-                             : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-      };
-      fetch(n_warp);
       ptx::mbar_wait(&tfull_bar[buf], use & 1);
       ptx::tc_fence_after();
+      if (p.dbg & 8) {
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty_bar[buf]);
+        continue;
+      }
 
       // ---- pass A: y = acc + bias + residual -> TMEM, running row statistics
       float r_mean = 0.f, r_m2 = 0.f;
 #pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
-        float v[32];
-        ptx::tmem_ld_32x32(taddr0 + c * 32, v);
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          const int rl = it * 4 + rsub;
-          ptx::sts_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4), pre[it].x, pre[it].y, pre[it].z, pre[it].w);
+        const int g = local * NCH + c;
+        uint32_t vr[32];
+        ptx::tmem_ld_32x32_nowait(taddr0 + c * 32, vr);
+        if (!(p.dbg & 4)) {                                  // residual block g has landed
+          const uint32_t bar = rbar + (uint32_t)(g & 1) * 8, parity = (uint32_t)(g >> 1) & 1u;
+          uint32_t done;
+          do {
+            asm volatile(
+                "{\n\t.reg .pred P1;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, P1;\n\t}\n"
+                : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+          } while (!done);
         }
-        __syncwarp();
-        if (c + 1 < NCH) fetch(n_warp + (c + 1) * 32);
+        ptx::tmem_ld_wait_on(vr);
+        float v[32];
+        const uint32_t rb = rbuf + (uint32_t)(g & 1) * 4096;
         float cs = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float4 r = ptx::lds_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4));
+          const float4 r = ptx::lds_v4(rb + lane * 128 + ((j ^ (lane & 7)) << 4));
           const float4 b = ptx::lds_v4(vec_s + (c * 32 + j * 4) * 4);
-          v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y; v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
+          v[4 * j] = __uint_as_float(vr[4 * j]) + r.x + b.x;
+          v[4 * j + 1] = __uint_as_float(vr[4 * j + 1]) + r.y + b.y;
+          v[4 * j + 2] = __uint_as_float(vr[4 * j + 2]) + r.z + b.z;
+          v[4 * j + 3] = __uint_as_float(vr[4 * j + 3]) + r.w + b.w;
           cs += (v[4 * j] + v[4 * j + 1]) + (v[4 * j + 2] + v[4 * j + 3]);
         }
+        ptx::fence_proxy_async();                            // our reads of the block precede the next TMA write
+        __syncwarp();
+        if (lane == 0 && g + 2 < total_blocks && !(p.dbg & 4)) issue_residual(g + 2);
         const float cm = cs * (1.0f / 32.0f);
         float cq = 0.f;
 #pragma unroll
@@ -211,7 +244,6 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         r_mean += delta * (nb / nt);
         r_m2 += cq + delta * delta * (na * nb / nt);
         ptx::tmem_st_32x32(taddr0 + c * 32, v);
-        __syncwarp();
       }
       ptx::tmem_st_wait();
 
@@ -221,12 +253,12 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(stats_s + off), "f"(r_mean), "f"(r_m2) : "memory");
       ptx::st_cluster_v2(stats_peer + off, r_mean, r_m2);
       __syncwarp();
-      if (lane == 0) {
+      if (lane == 0 && !(p.dbg & 1)) {
         const uint32_t bar_local = ptx::smem_u32(&stat_bar[par]);
         ptx::mbar_arrive_cluster(ptx::mapa(bar_local, rank));
         ptx::mbar_arrive_cluster(ptx::mapa(bar_local, rank ^ 1u));
       }
-      ptx::mbar_wait_cluster(&stat_bar[par], use & 1);
+      if (!(p.dbg & 1)) ptx::mbar_wait_cluster(&stat_bar[par], use & 1);
       float mean = 0.f, m2 = 0.f;
       {
         float pm[4], pq[4];
@@ -266,7 +298,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         for (int it = 0; it < 8; ++it) {
           const int rl = it * 4 + rsub, mm = m_warp + rl;
           const float4 w = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
-          if (mm < M) {
+          if (mm < M && !(p.dbg & 2)) {
             if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + (size_t)mm * p.ld_out + n) = w;
             if (p.out_h16) {
               uint2 pk;
@@ -305,11 +337,14 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   if (rc) return rc;
   rc = make_tmap_2d(&tw, W, 2 * BN, p.K, ldw, BN, fmt);
   if (rc) return rc;
+  CUtensorMap tr;
+  rc = make_tmap_2d_f32(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32);
+  if (rc) return rc;
   const int sms = num_sms();
   GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
   const int m_tiles = ceil_div(p.M, kLnBM);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  gemm_ln_tcgen05_kernel<BN><<<2 * clusters, kLnThreads, Cfg::kSmemBytes, stream>>>(ta, tw, p);
+  gemm_ln_tcgen05_kernel<BN><<<2 * clusters, kLnThreads, Cfg::kSmemBytes, stream>>>(ta, tw, tr, p);
   GD_LAUNCH_CHECK();
   return GD_OK;
 }
@@ -343,6 +378,14 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
   p.out_f32 = out_f32; p.ld_out = ld_out;
   p.out_h16 = out_h16; p.ld_out_h16 = ld_out_h16; p.h16_fmt = h16_fmt;
   p.eps = eps; p.M = M; p.K = K;
+  {
+    static int dbg = -1;
+    if (dbg < 0) {
+      const char* e = getenv("GD_LN_DBG");
+      dbg = e ? atoi(e) : 0;
+    }
+    p.dbg = dbg;
+  }
   p.idesc = ptx::umma_idesc_h16_f32(kLnBM, N / 2, fmt == GD_FP16);
   if (N == 512) return launch_gemm_ln<256>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
   return launch_gemm_ln<128>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
