@@ -8,11 +8,13 @@
 // A LayerNorm row spans the full N = d columns; one CTA's TMEM holds two 128 x BN fp32 accumulators (double
 // buffered), so a row is split over the TWO CTAs of a thread-block cluster (N = 2*BN, CTA rank r owns columns
 // [r*BN, (r+1)*BN)).  Per 128-row tile each epilogue thread owns one row x BN/2 columns:
-//   pass A  y = acc + bias + residual (residual fetched row-contiguously one block ahead and transposed
-//           through swizzled smem), running (mean, M2) by Chan's update, y written back to TMEM in place;
-//   exchange  the four partial (mean, M2) of a row -- 2 column halves x 2 CTAs -- are written to both CTAs'
-//           shared memory (st.shared::cluster) and published with one cluster-scope mbarrier per tile parity;
-//   pass B  z = (y - mean) * rstd * gamma + beta from TMEM, transposed through smem, row-contiguous stores.
+//   pass A  y = acc + bias + residual; the residual arrives as [32 x 32] fp32 TMA boxes in a per-warp ring, two
+//           blocks ahead of the consumer; running (mean, M2) by Chan's update; y written back to TMEM in place;
+//   exchange  the four partial (mean, M2) of a row -- 2 column halves x 2 CTAs -- go to both CTAs' shared memory
+//           with st.async, which completes transaction bytes on the destination's mbarrier (one expect_tx arrival
+//           per tile and CTA): data and signal travel together, no fence and no separate arrive;
+//   pass B  z = (y - mean) * rstd * gamma + beta from TMEM into swizzled staging blocks (fp32 128B swizzle, 16-bit
+//           64B swizzle), one TMA store per output and chunk (the hardware clips the ragged last tile).
 // Statistics are two-pass quality (no E[x^2] - mean^2 cancellation).
 #include <stdlib.h>
 
@@ -21,18 +23,23 @@
 
 namespace gd {
 
-constexpr int kLnBM = 128, kLnBK = 64, kLnEpiWarps = 8, kLnThreads = 320, kLnStages = 2;
+constexpr int kLnBM = 128, kLnBK = 64, kLnEpiWarps = 8, kLnThreads = 320;
 
-template <int BN>
+// ALIAS = false: per epilogue warp two residual blocks in flight (also across tile boundaries) plus separate
+// staging blocks.  ALIAS = true (one more operand stage for long K, main loop bound by the operand bytes in flight): the staging blocks alias the
+// two residual blocks, so the first residual blocks of a tile are only requested when the previous tile has left.
+template <int BN, int STAGES, bool ALIAS>
 struct LnCfg {
+  static constexpr bool kAlias = ALIAS;
+  static constexpr int kWarpRing = kAlias ? 2 * 4096 : 3 * 4096 + 2048;
   static constexpr int kABytes = kLnBM * kLnBK * 2;
   static constexpr int kBBytes = BN * kLnBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kRingBytes = kLnEpiWarps * 3 * 4096;     // per warp: 2 residual blocks in flight + 1 staging block
+  static constexpr int kRingBytes = kLnEpiWarps * kWarpRing;
   static constexpr int kVecBytes = 3 * BN * 4;                  // bias, gamma, beta slices of this CTA
   static constexpr int kStatBytes = 2 * 4 * kLnBM * 8;          // [parity][part][row] (mean, M2)
   static constexpr int kBarBytes = 512;
-  static constexpr int kSmemBytes = kLnStages * kStageBytes + kRingBytes + kVecBytes + kStatBytes + kBarBytes;
+  static constexpr int kSmemBytes = STAGES * kStageBytes + kRingBytes + kVecBytes + kStatBytes + kBarBytes;
   static constexpr int kTmemCols = 2 * BN;
 };
 
@@ -47,11 +54,14 @@ struct LnParams {
   int dbg;     // GD_LN_DBG diagnostics (results wrong): 1 no statistics exchange, 2 no global stores, 4 no residual, 8 no epilogue
 };
 
-template <int BN>
+template <int BN, int STAGES, bool ALIAS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
 gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                       const __grid_constant__ CUtensorMap tmap_res, const LnParams p) {
-  using Cfg = LnCfg<BN>;
+                       const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_o32,
+                       const __grid_constant__ CUtensorMap tmap_o16, const LnParams p) {
+  using Cfg = LnCfg<BN, STAGES, ALIAS>;
+  constexpr int kLnStages = STAGES;
+  constexpr bool kAlias = Cfg::kAlias;
   constexpr int N = 2 * BN;
   extern __shared__ __align__(1024) uint8_t smem[];
   if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
@@ -79,6 +89,8 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_w);
     ptx::prefetch_tensormap(&tmap_res);
+    ptx::prefetch_tensormap(&tmap_o32);
+    ptx::prefetch_tensormap(&tmap_o16);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < 2 * kLnEpiWarps; ++i) ptx::mbar_init(&res_bar[i], 1);
@@ -89,7 +101,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(&tfull_bar[b], 1);
       ptx::mbar_init(&tempty_bar[b], kLnEpiWarps);
-      ptx::mbar_init(&stat_bar[b], 2 * kLnEpiWarps);       // 8 local + 8 peer warps
+      ptx::mbar_init(&stat_bar[b], 1);                     // one expect_tx arrival per tile; the data are the transactions
     }
     ptx::fence_barrier_init();
   }
@@ -158,17 +170,20 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     const int half = ew >> 2;
     constexpr int CW = BN / 2;                               // columns per warp
     constexpr int NCH = CW / 32;
-    // per-warp ring: blocks 0/1 receive the residual ([32 rows x 32 fp32] TMA boxes, 128B swizzle: 16-byte chunk
-    // (c/4) ^ (r&7) of row r -- the layout of the staging block), two blocks in flight ahead of the consumer and
-    // across tile boundaries; block 2 is the staging block of pass B.
-    const uint32_t rbuf = ptx::smem_u32(ring) + (uint32_t)ew * (3 * 4096);
-    const uint32_t stg = rbuf + 2 * 4096;
+    // per-warp smem: blocks 0/1 receive the residual ([32 rows x 32 fp32] TMA boxes, 128B swizzle: 16-byte chunk
+    // (c/4) ^ (r&7) of row r), two blocks in flight ahead of the consumer and across tile boundaries; block 2
+    // (same layout) and a [32 x 32] 16-bit block (64B swizzle) stage the two outputs for the TMA stores of pass B.
+    const uint32_t rbuf = ptx::smem_u32(ring) + (uint32_t)ew * (kAlias ? 2 * 4096 : 3 * 4096);
+    const uint32_t stg = kAlias ? rbuf : rbuf + 2 * 4096;
+    const uint32_t stg16 =
+        kAlias ? rbuf + 4096 : ptx::smem_u32(ring) + (uint32_t)kLnEpiWarps * (3 * 4096) + (uint32_t)ew * 2048;
     const uint32_t rbar = ptx::smem_u32(&res_bar[2 * ew]);
     const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;      // this warp's bias slice
     const uint32_t stats_s = ptx::smem_u32(stats);
-    const uint32_t stats_peer = ptx::mapa(stats_s, rank ^ 1u);
+    const uint32_t stats_cl[2] = {ptx::mapa(stats_s, rank), ptx::mapa(stats_s, rank ^ 1u)};
+    const uint32_t sbar_s = ptx::smem_u32(stat_bar);
+    const uint32_t sbar_cl[2] = {ptx::mapa(sbar_s, rank), ptx::mapa(sbar_s, rank ^ 1u)};
     const uint32_t part = rank * 2u + (uint32_t)half;
-    const int c4 = lane & 7, rsub = lane >> 3;
     const int row_in_tile = quarter * 32 + lane;
     const int n_warp = n_cta + half * CW;
     const int my_tiles = (m_tiles - cluster_id + n_clusters - 1) / n_clusters;
@@ -188,8 +203,11 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
+      const uint32_t par = (uint32_t)(local & 1);
       const int m_warp = m_blk * kLnBM + quarter * 32;
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * CW);
+      // this tile's statistics: 4 partials x 128 rows x 8 bytes land on stat_bar[par] of each CTA
+      if (ew == 0 && lane == 0 && !(p.dbg & 8)) ptx::mbar_arrive_expect_tx(&stat_bar[par], 4 * kLnBM * 8);
       ptx::mbar_wait(&tfull_bar[buf], use & 1);
       ptx::tc_fence_after();
       if (p.dbg & 8) {
@@ -217,48 +235,61 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
           } while (!done);
         }
-        ptx::tmem_ld_wait_on(vr);
         float v[32];
         const uint32_t rb = rbuf + (uint32_t)(g & 1) * 4096;
-        float cs = 0.f;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < 8; ++j) {                        // residual + bias while the TMEM load is in flight
           const float4 r = ptx::lds_v4(rb + lane * 128 + ((j ^ (lane & 7)) << 4));
           const float4 b = ptx::lds_v4(vec_s + (c * 32 + j * 4) * 4);
-          v[4 * j] = __uint_as_float(vr[4 * j]) + r.x + b.x;
-          v[4 * j + 1] = __uint_as_float(vr[4 * j + 1]) + r.y + b.y;
-          v[4 * j + 2] = __uint_as_float(vr[4 * j + 2]) + r.z + b.z;
-          v[4 * j + 3] = __uint_as_float(vr[4 * j + 3]) + r.w + b.w;
-          cs += (v[4 * j] + v[4 * j + 1]) + (v[4 * j + 2] + v[4 * j + 3]);
+          v[4 * j] = r.x + b.x;
+          v[4 * j + 1] = r.y + b.y;
+          v[4 * j + 2] = r.z + b.z;
+          v[4 * j + 3] = r.w + b.w;
         }
         ptx::fence_proxy_async();                            // our reads of the block precede the next TMA write
         __syncwarp();
-        if (lane == 0 && g + 2 < total_blocks && !(p.dbg & 4)) issue_residual(g + 2);
-        const float cm = cs * (1.0f / 32.0f);
-        float cq = 0.f;
+        if (lane == 0 && g + 2 < total_blocks && !(p.dbg & 4) && (!kAlias || c + 2 < NCH)) issue_residual(g + 2);
+        ptx::tmem_ld_wait_on(vr);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) cq = fmaf(v[j] - cm, v[j] - cm, cq);
+        for (int j = 0; j < 8; ++j) {
+          v[4 * j] += __uint_as_float(vr[4 * j]);
+          v[4 * j + 1] += __uint_as_float(vr[4 * j + 1]);
+          v[4 * j + 2] += __uint_as_float(vr[4 * j + 2]);
+          v[4 * j + 3] += __uint_as_float(vr[4 * j + 3]);
+          s0 += v[4 * j];
+          s1 += v[4 * j + 1];
+          s2 += v[4 * j + 2];
+          s3 += v[4 * j + 3];
+        }
+        ptx::tmem_st_32x32(taddr0 + c * 32, v);
+        const float cm = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
+        float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d0 = v[4 * j] - cm, d1 = v[4 * j + 1] - cm, d2 = v[4 * j + 2] - cm, d3 = v[4 * j + 3] - cm;
+          q0 = fmaf(d0, d0, q0);
+          q1 = fmaf(d1, d1, q1);
+          q2 = fmaf(d2, d2, q2);
+          q3 = fmaf(d3, d3, q3);
+        }
+        const float cq = (q0 + q1) + (q2 + q3);
         // Chan: combine (c*32, r_mean, r_m2) with (32, cm, cq)
         const float na = (float)(c * 32), nb = 32.f, nt = na + nb;
         const float delta = cm - r_mean;
         r_mean += delta * (nb / nt);
         r_m2 += cq + delta * delta * (na * nb / nt);
-        ptx::tmem_st_32x32(taddr0 + c * 32, v);
       }
       ptx::tmem_st_wait();
 
-      // ---- exchange the partial statistics of this row with the other column half and the peer CTA
-      const uint32_t par = (uint32_t)(local & 1);
-      const uint32_t off = ((par * 4u + part) * kLnBM + (uint32_t)row_in_tile) * 8u;
-      asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(stats_s + off), "f"(r_mean), "f"(r_m2) : "memory");
-      ptx::st_cluster_v2(stats_peer + off, r_mean, r_m2);
-      __syncwarp();
-      if (lane == 0 && !(p.dbg & 1)) {
-        const uint32_t bar_local = ptx::smem_u32(&stat_bar[par]);
-        ptx::mbar_arrive_cluster(ptx::mapa(bar_local, rank));
-        ptx::mbar_arrive_cluster(ptx::mapa(bar_local, rank ^ 1u));
+      // ---- exchange: every thread sends its row's partial (mean, M2) to both CTAs of the cluster; the store
+      // itself completes transaction bytes on the destination's barrier (no fence, no separate arrive)
+      {
+        const uint32_t off = ((par * 4u + part) * kLnBM + (uint32_t)row_in_tile) * 8u;
+        ptx::st_async_v2(stats_cl[0] + off, r_mean, r_m2, sbar_cl[0] + par * 8u);
+        ptx::st_async_v2(stats_cl[1] + off, r_mean, r_m2, sbar_cl[1] + par * 8u);
       }
-      if (!(p.dbg & 1)) ptx::mbar_wait_cluster(&stat_bar[par], use & 1);
+      if (!(p.dbg & 1)) ptx::mbar_wait(&stat_bar[par], use & 1);
       float mean = 0.f, m2 = 0.f;
       {
         float pm[4], pq[4];
@@ -273,8 +304,9 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         for (int q = 0; q < 4; ++q) m2 += pq[q] + (float)CW * (pm[q] - mean) * (pm[q] - mean);
       }
       const float rstd = rsqrtf(m2 * (1.0f / (float)N) + p.eps);
+      const float shift = -mean * rstd;
 
-      // ---- pass B: normalise from TMEM, transpose through smem, row-contiguous stores
+      // ---- pass B: normalise from TMEM into the swizzled staging blocks, one TMA store per output and chunk
 #pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
         float v[32];
@@ -288,29 +320,43 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         for (int j = 0; j < 8; ++j) {
           const float4 g = ptx::lds_v4(vec_s + (BN + c * 32 + j * 4) * 4);
           const float4 b = ptx::lds_v4(vec_s + (2 * BN + c * 32 + j * 4) * 4);
-          ptx::sts_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4),
-                      (v[4 * j] - mean) * rstd * g.x + b.x, (v[4 * j + 1] - mean) * rstd * g.y + b.y,
-                      (v[4 * j + 2] - mean) * rstd * g.z + b.z, (v[4 * j + 3] - mean) * rstd * g.w + b.w);
+          v[4 * j] = fmaf(fmaf(v[4 * j], rstd, shift), g.x, b.x);
+          v[4 * j + 1] = fmaf(fmaf(v[4 * j + 1], rstd, shift), g.y, b.y);
+          v[4 * j + 2] = fmaf(fmaf(v[4 * j + 2], rstd, shift), g.z, b.z);
+          v[4 * j + 3] = fmaf(fmaf(v[4 * j + 3], rstd, shift), g.w, b.w);
         }
+        if (lane == 0) ptx::bulk_wait_read_all();            // the previous chunk's stores have read the staging
         __syncwarp();
-        const int n = n_warp + c * 32 + c4 * 4;
+        if (p.out_f32) {
 #pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          const int rl = it * 4 + rsub, mm = m_warp + rl;
-          const float4 w = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
-          if (mm < M && !(p.dbg & 2)) {
-            if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + (size_t)mm * p.ld_out + n) = w;
-            if (p.out_h16) {
-              uint2 pk;
-              pk.x = pack_h16x2(w.x, w.y, p.h16_fmt);
-              pk.y = pack_h16x2(w.z, w.w, p.h16_fmt);
-              *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(p.out_h16) + (size_t)mm * p.ld_out_h16 + n) = pk;
-            }
-          }
+          for (int j = 0; j < 8; ++j)
+            ptx::sts_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2],
+                        v[4 * j + 3]);
         }
+        if (p.out_h16) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            ptx::sts_v4u(stg16 + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4),
+                         pack_h16x2(v[8 * j], v[8 * j + 1], p.h16_fmt), pack_h16x2(v[8 * j + 2], v[8 * j + 3], p.h16_fmt),
+                         pack_h16x2(v[8 * j + 4], v[8 * j + 5], p.h16_fmt),
+                         pack_h16x2(v[8 * j + 6], v[8 * j + 7], p.h16_fmt));
+        }
+        ptx::fence_proxy_async();
         __syncwarp();
+        if (lane == 0 && !(p.dbg & 2)) {
+          if (p.out_f32) ptx::tma_store_2d(&tmap_o32, stg, n_warp + c * 32, m_warp);
+          if (p.out_h16) ptx::tma_store_2d(&tmap_o16, stg16, n_warp + c * 32, m_warp);
+          ptx::bulk_commit();
+        }
+      }
+      if (kAlias && lane == 0 && !(p.dbg & 4)) {             // staging has been read out: request the next tile's blocks
+        const int g = (local + 1) * NCH;
+        ptx::bulk_wait_read_all();
+        if (g < total_blocks) issue_residual(g);
+        if (g + 1 < total_blocks) issue_residual(g + 1);
       }
     }
+    if (lane == 0) ptx::bulk_wait_all();                     // global writes complete before the CTA retires
   }
 
   ptx::tc_fence_before();
@@ -322,13 +368,13 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   }
 }
 
-template <int BN>
+template <int BN, int STAGES, bool ALIAS>
 static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p,
                           cudaStream_t stream) {
-  using Cfg = LnCfg<BN>;
+  using Cfg = LnCfg<BN, STAGES, ALIAS>;
   static bool attr_set = false;
   if (!attr_set) {
-    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::kSmemBytes));
     attr_set = true;
   }
@@ -340,11 +386,20 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   CUtensorMap tr;
   rc = make_tmap_2d_f32(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32);
   if (rc) return rc;
+  CUtensorMap to32 = tr, to16 = tr;                          // placeholders when an output is absent (never used)
+  if (p.out_f32) {
+    rc = make_tmap_2d_f32(&to32, p.out_f32, p.M, 2 * BN, p.ld_out, 32);
+    if (rc) return rc;
+  }
+  if (p.out_h16) {
+    rc = make_tmap_2d_h16_sw64(&to16, p.out_h16, p.M, 2 * BN, p.ld_out_h16, 32, p.h16_fmt);
+    if (rc) return rc;
+  }
   const int sms = num_sms();
   GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
   const int m_tiles = ceil_div(p.M, kLnBM);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  gemm_ln_tcgen05_kernel<BN><<<2 * clusters, kLnThreads, Cfg::kSmemBytes, stream>>>(ta, tw, tr, p);
+  gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS><<<2 * clusters, kLnThreads, Cfg::kSmemBytes, stream>>>(ta, tw, tr, to32, to16, p);
   GD_LAUNCH_CHECK();
   return GD_OK;
 }
@@ -370,8 +425,8 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
   GD_REQUIRE(al16(A) && al16(W) && al16(residual) && (!out_f32 || al16(out_f32)) && (!out_h16 || al16(out_h16)),
              "gd_gemm_h16_ln: operands must be 16-byte aligned");
   GD_REQUIRE(ld_res >= N && ld_res % 4 == 0 && (!out_f32 || (ld_out >= N && ld_out % 4 == 0)) &&
-                 (!out_h16 || (ld_out_h16 >= N && ld_out_h16 % 4 == 0)),
-             "gd_gemm_h16_ln: leading dimensions must be >= N and multiples of 4");
+                 (!out_h16 || (ld_out_h16 >= N && ld_out_h16 % 8 == 0)),
+             "gd_gemm_h16_ln: leading dimensions must be >= N and multiples of 4 (16-bit output: 8)");
   LnParams p;
   p.bias = bias; p.gamma = gamma; p.beta = beta;
   p.residual = residual; p.ld_res = ld_res;
@@ -387,6 +442,14 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
     p.dbg = dbg;
   }
   p.idesc = ptx::umma_idesc_h16_f32(kLnBM, N / 2, fmt == GD_FP16);
-  if (N == 512) return launch_gemm_ln<256>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
-  return launch_gemm_ln<128>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
+  static int force_stages = -1;
+  if (force_stages < 0) {
+    const char* e = getenv("GD_LN_STAGES");
+    force_stages = e ? atoi(e) : 0;
+  }
+  const bool deep = force_stages ? force_stages > 2 : true;
+  if (N == 512)
+    return deep ? launch_gemm_ln<256, 3, true>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream)
+                : launch_gemm_ln<256, 2, false>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
+  return launch_gemm_ln<128, 3, false>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
 }

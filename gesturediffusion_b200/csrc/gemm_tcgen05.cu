@@ -421,6 +421,29 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* base, int rows, int cols, int
   return GD_OK;
 }
 
+// 2D 16-bit row-major [rows, cols]; box = [box_rows, 32 cols] (64-byte rows), 64B swizzle: 16-byte chunk c of box
+// row r sits at chunk c ^ ((r >> 1) & 3).
+int make_tmap_2d_h16_sw64(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    return GD_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, fmt == GD_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (16-bit, 64B swizzle) failed with CUresult %d (rows=%d cols=%d ld=%d)", (int)r,
+              rows, cols, ld);
+    return GD_ERR_CUDA;
+  }
+  return GD_OK;
+}
+
 // 2D bf16 row-major [rows, cols] with row stride ld elements; box = [box_rows, 64 cols], SW128.
 int make_tmap_2d(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt) {
   EncodeTiledFn enc = get_encode_fn();

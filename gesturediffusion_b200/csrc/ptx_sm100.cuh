@@ -11,6 +11,7 @@ namespace gd {
 // 2D 16-bit row-major tensor [rows, cols] with row stride ld elements; box = [box_rows, 64 cols], 128B swizzle.
 int make_tmap_2d(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt);
 int make_tmap_2d_f32(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows);
+int make_tmap_2d_h16_sw64(CUtensorMap* out, const void* base, int rows, int cols, int ld, int box_rows, int fmt);
 int num_sms();
 
 namespace ptx {
@@ -278,6 +279,14 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
 }
 __device__ __forceinline__ void st_cluster_v2(uint32_t cluster_addr, float a, float b) {
   asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(cluster_addr), "f"(a), "f"(b) : "memory");
+}
+// 8-byte store into (possibly remote) shared memory of the cluster that completes 8 transaction bytes on an
+// mbarrier of the SAME destination CTA: data and signal travel together, no fence on the sender.
+__device__ __forceinline__ void st_async_v2(uint32_t cluster_addr, float a, float b, uint32_t cluster_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(
+                   cluster_addr),
+               "f"(a), "f"(b), "r"(cluster_bar)
+               : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");

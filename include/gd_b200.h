@@ -88,7 +88,8 @@ int gd_gemm_f32(const float* A, int32_t lda, const float* W, int32_t ldw,
  * out_f32 [M, ld_out] and / or out_h16 [M, ld_out_h16] (h16_fmt).  N must be 256 or 512 (= 2 x the per-CTA
  * accumulator width: a row is normalised across the two CTAs of a thread-block cluster through distributed
  * shared memory); other widths return GD_ERR_UNSUPPORTED and callers use gd_gemm_h16 + gd_layernorm.
- * residual may alias out_f32 (each element is read before it is written, by the same thread). */
+ * residual may alias out_f32 (each element is read before it is written, by the same warp).  ld_res / ld_out are
+ * multiples of 4 elements, ld_out_h16 of 8 (the outputs leave through TMA stores). */
 int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
                    int32_t fmt, const float* bias, const float* residual, int32_t ld_res,
                    const float* gamma, const float* beta, float eps, float* out_f32, int32_t ld_out,
