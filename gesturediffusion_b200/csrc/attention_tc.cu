@@ -79,6 +79,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::grid_dep_wait();                                      // prologue above overlaps the previous kernel's tail
+  ptx::grid_dep_launch();
 
   // unit u -> (item, query tile, kv buffer); both kv-buffer use counts equal u >> 1
   auto item_of = [&](int u) { return (int)blockIdx.x + (n_qt == 2 ? (u >> 1) : u) * (int)gridDim.x; };
@@ -324,7 +326,7 @@ int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_head
   const int sms = num_sms();
   GD_REQUIRE(sms > 0, "gd_attention_h16: cannot query the SM count");
   const int grid = p.n_items < sms ? p.n_items : sms;
-  attention_tc_kernel<<<grid, kAtThreads, kAtSmemBytes, stream>>>(tq, tkv, p);
+  GD_CUDA_OK(launch_pdl(attention_tc_kernel, dim3(grid), dim3(kAtThreads), kAtSmemBytes, stream, tq, tkv, p));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

@@ -1,6 +1,7 @@
 // common.cuh -- shared device/host helpers for the gd_b200 kernels (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
@@ -31,6 +32,33 @@ extern std::atomic<long long> g_launches;
       return GD_ERR_CUDA;                                                             \
     }                                                                                 \
   } while (0)
+
+// GD_PDL=0 turns programmatic dependent launch off (kernels then serialise the ordinary way).
+inline bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("GD_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on != 0;
+}
+// Launch with the programmatic-stream-serialization attribute: the grid may be scheduled while the previous
+// kernel of the stream drains; the kernel itself orders its global accesses with ptx::grid_dep_wait().
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 #define GD_LAUNCH_CHECK()                                                             \
   do {                                                                                \

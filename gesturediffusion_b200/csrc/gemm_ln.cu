@@ -116,6 +116,8 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   ptx::cluster_sync_all();                                   // peer's barriers are initialised before any remote arrive
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::grid_dep_wait();                                      // prologue above overlaps the previous kernel's tail
+  ptx::grid_dep_launch();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -399,7 +401,8 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
   const int m_tiles = ceil_div(p.M, kLnBM);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS><<<2 * clusters, kLnThreads, Cfg::kSmemBytes, stream>>>(ta, tw, tr, to32, to16, p);
+  GD_CUDA_OK(launch_pdl(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS>, dim3(2 * clusters), dim3(kLnThreads), Cfg::kSmemBytes,
+                        stream, ta, tw, tr, to32, to16, p));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

@@ -35,7 +35,7 @@ constexpr int kGemmThreads = (2 + kEpiWarps) * 32;
 // MMA issue (tensor pipe ~50 % idle with all operands resident).
 constexpr int kProducerWarp = kEpiWarps, kMmaWarp = kEpiWarps + 1;
 
-enum { EPI_GENERIC = 0, EPI_BIAS_H16 = 1, EPI_BIAS_GELU_H16 = 2, EPI_BIAS_RES_F32 = 3 };
+enum { EPI_GENERIC = 0, EPI_BIAS_H16 = 1, EPI_BIAS_GELU_H16 = 2, EPI_BIAS_RES_F32 = 3, EPI_QUAD = 4, EPI_OUT_T = 5 };
 
 // CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x BN tile;
 // each CTA stages its own 128 rows of A and HALF of the W tile, the pair's MMA (M = 256) reads both halves, so the
@@ -170,6 +170,8 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   if constexpr (CG == 2) ptx::cluster_sync_all();            // peer barriers initialised, both TMEM allocations done
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::grid_dep_wait();                                      // prologue above overlaps the previous kernel's tail
+  ptx::grid_dep_launch();
 
   if (warp == kProducerWarp) {
     // ------------------------------------------------------------------ TMA producer
@@ -262,6 +264,90 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           float v[32];
           ptx::tmem_ld_32x32(taddr0 + c, v);
           if (m_warp + lane < M) epilogue_row_chunk<32>(ep, m_warp + lane, n0, N, v);
+        }
+      } else if constexpr (EPI == EPI_QUAD) {
+        // Every linear gdEpilogue feature (bias, row table, per-sequence bias, residual, row map, copies; no
+        // activation, no out_t) on row-contiguous quads: TMEM -> registers (row = lane) -> this warp's swizzled
+        // staging block -> lane (it, c4) takes columns 4*c4 .. 4*c4+3 of row 4*it + lane/8, so table, residual and
+        // output accesses are full 128-byte lines.  The row index arithmetic (three integer divisions) is done once
+        // per tile by the lane that owns the row in TMEM and handed to the quad's lane with a shuffle.
+        const int c4 = lane & 7, rsub = lane >> 3;
+        int tabrow_l, outrow_l, seqrow_l;                    // of row `lane`; fetched per quad with a shuffle
+        {
+          const int mm = m_warp + lane;
+          tabrow_l = ep.rowtab ? (mm % ep.tab_period) + ep.tab_offset : 0;
+          seqrow_l = ep.seqbias ? mm / ep.seq_rows : 0;
+          const int mapped = ep.map_t > 0 ? (mm / ep.map_t) * ep.map_s + ep.map_off + (mm % ep.map_t) : mm;
+          outrow_l = mm < M ? mapped : -1;
+        }
+        const int ncopy = ep.dup > 1 ? ep.dup : 1;
+        ptx::mbar_wait(&tfull_bar[buf], use & 1);
+        ptx::tc_fence_after();
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
+#pragma unroll 1
+        for (int c = 0; c < kColsPerWarp; c += 32) {
+          const int n0 = n_base + c;
+          if (n0 >= N) break;                                // warp-uniform
+          uint32_t v[32];
+          ptx::tmem_ld_32x32_nowait(taddr0 + c, v);
+          const int n = n0 + c4 * 4;
+          const bool col_ok = n < N;                         // N % 4 == 0: a quad is inside or outside
+          float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ep.bias && col_ok) bias4 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
+          ptx::tmem_ld_wait_on(v);
+          epi_stage(stg, lane, v);
+          __syncwarp();
+#pragma unroll 4
+          for (int it = 0; it < 8; ++it) {
+            const int rl = it * 4 + rsub;
+            float4 w = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
+            const int outrow = __shfl_sync(0xffffffffu, outrow_l, rl);
+            const int tabrow = __shfl_sync(0xffffffffu, tabrow_l, rl);
+            const int seqrow = __shfl_sync(0xffffffffu, seqrow_l, rl);
+            if (outrow < 0 || !col_ok) continue;
+            f4_add(w, bias4);
+            if (ep.rowtab) f4_add(w, __ldg(reinterpret_cast<const float4*>(ep.rowtab + (size_t)tabrow * ep.ld_tab + n)));
+            for (int cp = 0; cp < ncopy; ++cp) {
+              float4 o = w;
+              if (ep.seqbias)
+                f4_add(o, __ldg(reinterpret_cast<const float4*>(
+                              ep.seqbias + (size_t)(cp * ep.seq_count + seqrow) * ep.ld_seq + n)));
+              const size_t r = (size_t)outrow + (size_t)cp * ep.dup_row_stride;
+              if (ep.residual) f4_add(o, *reinterpret_cast<const float4*>(ep.residual + r * ep.ld_res + n));
+              if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + r * ep.ld_out + n) = o;
+              if (ep.out_h16) {
+                uint2 pk;
+                pk.x = pack_h16x2(o.x, o.y, ep.h16_fmt);
+                pk.y = pack_h16x2(o.z, o.w, ep.h16_fmt);
+                *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(ep.out_h16) + r * ep.ld_out_h16 + n) = pk;
+              }
+            }
+          }
+          __syncwarp();
+        }
+      } else if constexpr (EPI == EPI_OUT_T) {
+        // bias + transposed fp32 output out_t[seq][n][s - t_skip] (OutputProcess + output[1:] + permute): in the
+        // TMEM layout lane = row = consecutive frames of one sequence, so each column's store is one contiguous run.
+        const int mm = m_warp + lane;
+        const int seq = mm / ep.t_s, s_in = mm - seq * ep.t_s;
+        const bool row_ok = mm < M && s_in >= ep.t_skip;
+        float* orow = ep.out_t + (size_t)seq * N * ep.t_t + (s_in - ep.t_skip);
+        ptx::mbar_wait(&tfull_bar[buf], use & 1);
+        ptx::tc_fence_after();
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
+#pragma unroll 1
+        for (int c = 0; c < kColsPerWarp; c += 32) {
+          const int n0 = n_base + c;
+          if (n0 >= N) break;                                // warp-uniform
+          uint32_t v[32];
+          ptx::tmem_ld_32x32_nowait(taddr0 + c, v);
+          ptx::tmem_ld_wait_on(v);
+          if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (n0 + i < N)
+                orow[(size_t)(n0 + i) * ep.t_t] = __uint_as_float(v[i]) + (ep.bias ? __ldg(ep.bias + n0 + i) : 0.f);
+          }
         }
       } else if constexpr (EPI == EPI_BIAS_H16 || EPI == EPI_BIAS_GELU_H16) {
         // 16-bit outputs leave through TMA stores: per warp and 64 columns, TMEM -> registers (row = lane) ->
@@ -479,18 +565,29 @@ int num_sms() {
 // Which compile-time epilogue serves this gdEpilogue (EPI_GENERIC handles everything).
 static int pick_epilogue(const gdEpilogue* ep, int N) {
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  if (N % 32 != 0 || !ep->bias || !al16(ep->bias) || ep->rowtab || ep->seqbias || ep->map_t > 0 || ep->dup > 1 ||
-      ep->out_t)
-    return EPI_GENERIC;
+  if (ep->out_t) {
+    const bool plain = !ep->rowtab && !ep->seqbias && !ep->residual && ep->act == GD_ACT_NONE && ep->dup <= 1 &&
+                       ep->map_t <= 0 && !ep->out_f32 && !ep->out_h16;
+    return plain ? EPI_OUT_T : EPI_GENERIC;
+  }
+  const bool quad_ok = N % 4 == 0 && ep->act == GD_ACT_NONE && (!ep->bias || al16(ep->bias)) &&
+                       (!ep->rowtab || (al16(ep->rowtab) && ep->ld_tab % 4 == 0)) &&
+                       (!ep->seqbias || (al16(ep->seqbias) && ep->ld_seq % 4 == 0)) &&
+                       (!ep->residual || (al16(ep->residual) && ep->ld_res % 4 == 0)) &&
+                       (!ep->out_f32 || (al16(ep->out_f32) && ep->ld_out % 4 == 0)) &&
+                       (!ep->out_h16 || (al16(ep->out_h16) && ep->ld_out_h16 % 4 == 0));
+  const int fallback = quad_ok ? EPI_QUAD : EPI_GENERIC;
+  if (N % 32 != 0 || !ep->bias || !al16(ep->bias) || ep->rowtab || ep->seqbias || ep->map_t > 0 || ep->dup > 1)
+    return fallback;
   if (ep->out_h16 && !ep->out_f32 && !ep->residual && al16(ep->out_h16) && ep->ld_out_h16 % 8 == 0) {
     if (ep->act == GD_ACT_NONE) return EPI_BIAS_H16;
     if (ep->act == GD_ACT_GELU_ERF) return EPI_BIAS_GELU_H16;
-    return EPI_GENERIC;
+    return fallback;
   }
   if (ep->out_f32 && !ep->out_h16 && ep->residual && ep->act == GD_ACT_NONE && al16(ep->out_f32) &&
       al16(ep->residual) && ep->ld_out % 4 == 0 && ep->ld_res % 4 == 0)
     return EPI_BIAS_RES_F32;
-  return EPI_GENERIC;
+  return fallback;
 }
 
 // GD_GEMM_DBG (diagnostics only, results are wrong): bit 0 = skip the epilogue work, bit 1 = skip the MMAs,
@@ -528,7 +625,8 @@ static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, in
   const int workers = tiles < g_num_sms / CG ? tiles : g_num_sms / CG;
   const uint32_t idesc = ptx::umma_idesc_h16_f32(kBM * CG, BN, fmt == GD_FP16);
   if (CG == 1) {
-    gemm_h16_tcgen05_kernel<BN, EPI, CG><<<workers, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tw, to, M, N, K, idesc, *ep, gemm_dbg());
+    GD_CUDA_OK(launch_pdl(gemm_h16_tcgen05_kernel<BN, EPI, CG>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
+                          ta, tw, to, M, N, K, idesc, *ep, gemm_dbg()));
   } else {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(workers * CG);
@@ -568,7 +666,9 @@ extern "C" int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ld
   }
   // Tile choice: BN=256 halves A re-reads and epilogue barrier traffic; BN=128 gives finer waves.
   const long tiles256 = (long)ceil_div(M, kBM) * ceil_div(N, 256);
-  const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms);
+  // (unless the last 256-wide column tile would be mostly padding, e.g. N = 263)
+  const int pad256 = ceil_div(N, 256) * 256 - N, pad128 = ceil_div(N, 128) * 128 - N;
+  const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms) && (pad256 <= pad128);
   const int epi = pick_epilogue(ep, N);
   cudaStream_t st = (cudaStream_t)stream;
   // CTA pairs (cta_group::2, 256 x 256 tiles) are implemented and parity-tested but opt-in (GD_GEMM_CG=2): at the
@@ -590,6 +690,8 @@ extern "C" int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ld
     GD_GEMM_CASE(EPI_BIAS_H16)
     GD_GEMM_CASE(EPI_BIAS_GELU_H16)
     GD_GEMM_CASE(EPI_BIAS_RES_F32)
+    GD_GEMM_CASE(EPI_QUAD)
+    GD_GEMM_CASE(EPI_OUT_T)
     default: break;
   }
   return use256 ? launch_gemm<256, EPI_GENERIC>(A, lda, W, ldw, M, N, K, fmt, ep, st)

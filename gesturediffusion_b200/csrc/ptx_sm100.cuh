@@ -16,6 +16,12 @@ int num_sms();
 
 namespace ptx {
 
+// Programmatic dependent launch: a kernel launched with the stream-serialization attribute may start while its
+// predecessor drains; nothing the predecessor wrote may be touched (and nothing it reads overwritten) before
+// grid_dep_wait().  Both are no-ops for a kernel launched the ordinary way.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

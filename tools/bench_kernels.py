@@ -110,6 +110,21 @@ def main():
     if on("f2ln"):
         rec("gemm ffn2+LN N=512 K=1024 ->f32+h16", timed(lambda i: K.gemm_ln(Hh[i % ns], w_2, b_2, X32[i % ns], gam, bet, out_f32=X32[i % ns], out_h16=Xa[i % ns]), a.iters),
             flops=2.0 * M * d * F, nbytes=M * F * esz + M * d * (4 + 4 + esz))
+    if on("inproj") or on("outproj"):
+        B, T, nb, J, kin = nseq // 2, S - 1, 2, 263, 296
+        a_in = [rnd(B * T, kin, dtype=act) for _ in range(ns)]
+        w_in, b_in, pe = rnd(d, kin, dtype=act, scale=0.05), rnd(d), rnd(5000, d)
+        w_out, b_out = rnd(J, d, dtype=act, scale=0.04), rnd(J)
+        OUT = [torch.empty(nb * B, J, T, device=dev) for _ in range(ns)]
+        if on("inproj"):
+            rec("gemm in   N=512 K=289 pe dup2 ->f32+h16", timed(lambda i: K.gemm(
+                a_in[i % ns], w_in, K.epilogue(bias=b_in, rowtab=pe, tab_period=T, tab_offset=1, rowmap=(T, S, 1), dup=nb,
+                                               dup_row_stride=B * S, out_f32=X32[i % ns], out_h16=Xa[i % ns]), K=289), a.iters),
+                flops=2.0 * B * T * d * 289, nbytes=B * T * kin * esz + nb * B * T * d * (4 + esz))
+        if on("outproj"):
+            rec("gemm out  N=263 K=512 ->f32 [B,J,T]", timed(lambda i: K.gemm(
+                Xa[i % ns], w_out, K.epilogue(bias=b_out, out_t=OUT[i % ns], t_s=S, t_t=T, t_skip=1), K=d), a.iters),
+                flops=2.0 * M * J * d, nbytes=M * d * esz + nb * B * J * T * 4)
     print(json.dumps({"rows": M, "S": S, "us": out}))
 
 
