@@ -360,3 +360,6 @@ if __name__ == "__main__":
         run_reference(a)
     else:
         run_b200(a)
+        import torch.distributed as _dist
+        if _dist.is_available() and _dist.is_initialized():
+            _dist.destroy_process_group()

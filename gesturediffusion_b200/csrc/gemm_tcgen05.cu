@@ -351,15 +351,19 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
         }
       } else if constexpr (EPI == EPI_BIAS_H16 || EPI == EPI_BIAS_GELU_H16) {
         // 16-bit outputs leave through TMA stores: per warp and 64 columns, TMEM -> registers (row = lane) ->
-        // + bias (slice of the tile in smem) [-> GELU] -> 16-bit pairs -> this warp's 32 x 128 B staging block in the
+        // + bias [-> GELU] -> 16-bit pairs -> this warp's 32 x 128 B staging block in the
         // 128B-swizzle layout -> one cp.async.bulk.tensor store of a [32 rows x 64 columns] box.  The stores are
         // asynchronous full-line writes issued by one lane; rows >= M and columns >= N are clipped by the TMA.
-        {
-          const int t = threadIdx.x;                         // 256 epilogue threads load the tile's bias slice
-          if (t < BN) bias_s[(local & 1) * BN + t] = (n_blk * BN + t < N) ? __ldg(ep.bias + n_blk * BN + t) : 0.f;
-          ptx::named_bar_sync(1, kEpiWarps * 32);
-        }
-        const uint32_t bs = ptx::smem_u32(bias_s) + (uint32_t)((local & 1) * BN + half * kColsPerWarp) * 4;
+        // The bias of a 64-column block is fetched as 16 warp-uniform 16-byte loads (one sector each, L1 hits after
+        // the first tile of a column block) into registers BEFORE the wait on the accumulator / the TMEM load.
+        auto load_bias = [&](int n0, float4 (&bq)[16]) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            bq[j] = (n0 + 4 * j < N) ? __ldg(reinterpret_cast<const float4*>(ep.bias + n0 + 4 * j))
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        float4 bq[16];
+        if (n_base < N) load_bias(n_base, bq);
         ptx::mbar_wait(&tfull_bar[buf], use & 1);
         ptx::tc_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
@@ -370,6 +374,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           uint32_t v0[32], v1[32];
           ptx::tmem_ld_32x32_nowait(taddr0 + r * 64, v0);
           ptx::tmem_ld_32x32_nowait(taddr0 + r * 64 + 32, v1);
+          if (r > 0) load_bias(n0, bq);
           if (lane == 0) ptx::bulk_wait_read_all();          // the previous store has finished reading the staging
           __syncwarp();
           ptx::tmem_ld_wait_on(v0);
@@ -377,8 +382,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
 #pragma unroll
           for (int j = 0; j < 8; ++j) {                      // 16-byte chunk j = columns 8j .. 8j+7 of the 64
             const uint32_t* src = (j < 4) ? &v0[8 * j] : &v1[8 * (j - 4)];
-            const float4 b0 = ptx::lds_v4(bs + (uint32_t)(r * 64 + j * 8) * 4);
-            const float4 b1 = ptx::lds_v4(bs + (uint32_t)(r * 64 + j * 8 + 4) * 4);
+            const float4 b0 = bq[2 * j], b1 = bq[2 * j + 1];
             float w[8];
             w[0] = __uint_as_float(src[0]) + b0.x; w[1] = __uint_as_float(src[1]) + b0.y;
             w[2] = __uint_as_float(src[2]) + b0.z; w[3] = __uint_as_float(src[3]) + b0.w;

@@ -30,7 +30,10 @@ def init_process_group(backend=None):
     if backend == "nccl":
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    kw = {}
+    if backend == "nccl":
+        kw["device_id"] = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
     return rank, world
 
 
