@@ -299,21 +299,39 @@ def run_b200(args):
         dif.use_cuda_graph = True
         tot = sum(t for _, t in summ.values())
         breakdown = sorted(((n, dict(m), c, t) for (n, m), (c, t) in summ.items()), key=lambda r: -r[3])
-        gemm = [(m, c, t) for n, m, c, t in breakdown if n == "gemm_h16"]
+        gemm = [(n, m, c, t) for n, m, c, t in breakdown if n in ("gemm_h16", "gemm_ln_h16")]
         if gemm:
-            fl = sum(2.0 * m["M"] * m["N"] * m["K"] * c for m, c, t in gemm)
-            tt = sum(t for m, c, t in gemm)
-            top = gemm[0]
-            ach = 2.0 * top[0]["M"] * top[0]["N"] * top[0]["K"] * top[1] / (top[2] * 1e-3) / 1e12
+            # algorithmic work per launch: 2MNK flops; bytes = A (16 bit) + outputs (+ fp32 residual for
+            # the GEMM+LayerNorm kernel); the weights stay L2-resident and are not counted
+            def algo(n, m):
+                fl = 2.0 * m["M"] * m["N"] * m["K"]
+                by = m["M"] * m["K"] * 2.0 + (m["M"] * m["N"] * (4.0 + 4.0 + 2.0) if n == "gemm_ln_h16"
+                                              else m["M"] * m["N"] * 2.0)
+                return fl, by
+            fl_all = sum(algo(n, m)[0] * c for n, m, c, t in gemm)
+            tt = sum(t for n, m, c, t in gemm)
+            n0, m0, c0, t0 = gemm[0]                           # the kernel with the largest share of the step
+            fl0, by0 = algo(n0, m0)
+            sec = t0 / c0 * 1e-3
+            hbm_bound = by0 / (peaks["hbm_gbs"] * 1e9) > fl0 / (peaks["tflops_sustained"] * 1e12)
+            label = "%s M=%d N=%d K=%d" % ("gemm_ln_tcgen05_kernel" if n0 == "gemm_ln_h16" else "gemm_h16_tcgen05_kernel",
+                                           m0["M"], m0["N"], m0["K"])
             traffic = None
             tpath = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(tpath):
-                traffic = json.load(open(tpath)).get("gemm_h16_dominant_dram_bytes_per_launch")
-            roof = {"bound": "tensor", "kernel": "gemm_h16_tcgen05_kernel M=%d N=%d K=%d" % (top[0]["M"], top[0]["N"], top[0]["K"]),
-                    "achieved": ach, "peak": peaks["tflops_sustained"], "unit": "TFLOP/s",
-                    "frac": ach / peaks["tflops_sustained"], "traffic": traffic, "peak_source": peaks["source"],
-                    "launch_ms": top[2] / top[1], "share_of_step": top[2] / tot,
-                    "all_gemms": {"achieved": fl / (tt * 1e-3) / 1e12, "share_of_step": tt / tot}}
+                traffic = json.load(open(tpath)).get(label, {}).get("dram_bytes_per_launch")
+            if hbm_bound:
+                ach, peak, unit = by0 / sec / 1e9, peaks["hbm_gbs"], "GB/s"
+            else:
+                ach, peak, unit = fl0 / sec / 1e12, peaks["tflops_sustained"], "TFLOP/s"
+            roof = {"bound": "hbm" if hbm_bound else "tensor", "kernel": label, "achieved": ach, "peak": peak,
+                    "unit": unit, "frac": ach / peak, "traffic": traffic, "peak_source": peaks["source"],
+                    "launch_ms": t0 / c0, "share_of_step": t0 / tot, "algorithmic_bytes_per_launch": by0,
+                    "algorithmic_flops_per_launch": fl0,
+                    "tensor_tflops_same_kernel": fl0 / sec / 1e12,
+                    "all_gemms": {"achieved": fl_all / (tt * 1e-3) / 1e12, "unit": "TFLOP/s",
+                                  "frac_of_tensor_peak": fl_all / (tt * 1e-3) / 1e12 / peaks["tflops_sustained"],
+                                  "share_of_step": tt / tot}}
         if args.profile_out:
             with open(args.profile_out, "w") as fh:
                 json.dump({"workload": workload_name(args, cfg, B, T, D, use_cfg), "eager_denoise_steps": 6,
