@@ -125,6 +125,18 @@ def main():
             rec("gemm out  N=263 K=512 ->f32 [B,J,T]", timed(lambda i: K.gemm(
                 Xa[i % ns], w_out, K.epilogue(bias=b_out, out_t=OUT[i % ns], t_s=S, t_t=T, t_skip=1), K=d), a.iters),
                 flops=2.0 * M * J * d, nbytes=M * d * esz + nb * B * J * T * 4)
+    if on("lattn"):
+        nsq, T2, hd = 256, 120, 8
+        e2 = d // hd
+        pos = torch.arange(T2 + 1, device=dev, dtype=torch.float32)[:, None]
+        inv = 1.0 / (10000 ** (torch.arange(0, e2, 2, device=dev, dtype=torch.float32) / e2))
+        ang = torch.cat([pos * inv, pos * inv], dim=1)
+        rc, rs = ang.cos().contiguous(), ang.sin().contiguous()
+        ZL = [rnd(nsq * T2, d) for _ in range(ns)]
+        XO = [torch.zeros(nsq * (T2 + 1), d, device=dev) for _ in range(ns)]
+        XH = [torch.zeros(nsq * (T2 + 1), d, device=dev, dtype=act) for _ in range(ns)]
+        rec("local attention T=120 e=64 w=10", timed(lambda i: K.local_attention(ZL[i % ns], rc, rs, XO[i % ns], XH[i % ns], nsq, T2, d, hd, 10), a.iters),
+            nbytes=nsq * T2 * d * (4 + 4 + esz))
     print(json.dumps({"rows": M, "S": S, "us": out}))
 
 
