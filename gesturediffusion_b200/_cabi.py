@@ -15,7 +15,7 @@ GD_F32, GD_BF16, GD_FP16 = 0, 1, 2
 EXPORTED_SYMBOLS = [
     "gd_abi_version", "gd_last_error", "gd_gemm_h16", "gd_gemm_f32", "gd_gemm_h16_ln", "gd_attention_h16",
     "gd_attention_f32", "gd_layernorm", "gd_local_attention", "gd_cond_tokens", "gd_posterior_step",
-    "gd_pack_rows", "gd_q_sample", "gd_philox_normal", "gd_set_loop_state", "gd_launch_count",
+    "gd_pack_rows", "gd_unnormalize_split", "gd_q_sample", "gd_philox_normal", "gd_set_loop_state", "gd_launch_count",
 ]
 
 _p, _i32, _i64, _u64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_float
@@ -48,6 +48,7 @@ class GdPosteriorArgs(C.Structure):
         ("B", _i32), ("J", _i32), ("T", _i32),
         ("eps_mode", _i32), ("clip", _i32), ("const_noise", _i32),
         ("seed", _u64), ("sample_base", _i64),
+        ("seed_dev", _p), ("ddim", _i32),
     ]
 
 
@@ -83,6 +84,7 @@ def load():
         "gd_cond_tokens": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _p],
         "gd_posterior_step": [PA, _p],
         "gd_pack_rows": [_p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p],
+        "gd_unnormalize_split": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _p],
         "gd_q_sample": [_p, _p, _p, _p, _i32, _p, _i64, _p],
         "gd_philox_normal": [_p, _i32, _i32, _i32, _u64, _i64, _i32, _p],
         "gd_set_loop_state": [_p, _p, _p, _i32, _i32, _p],

@@ -52,13 +52,21 @@ constexpr int PS_THREADS = 256;
 
 __device__ __forceinline__ float post_one(float c, float u, float sc, bool has_u, float xt, float nz, float coef1,
                                           float coef2, float sigma, float c_recip, float c_recipm1, int eps_mode,
-                                          int clip, bool has_mask, bool msk, float inp, float* x0_out,
+                                          int ddim, int clip, bool has_mask, bool msk, float inp, float* x0_out,
                                           float* mean_out) {
   float out = has_u ? (u + sc * (c - u)) : c;
   if (has_mask) out = msk ? inp : out;
   float x0 = eps_mode ? (c_recip * xt - c_recipm1 * out) : out;
   if (clip) x0 = fminf(fmaxf(x0, -1.0f), 1.0f);
-  const float mean = coef1 * x0 + coef2 * xt;
+  float mean;
+  if (ddim) {
+    // ddim_sample (gaussian_diffusion.py:761-782): eps re-derived from pred_xstart (:763), eq. 12 with
+    // coef1 = sqrt(alpha_bar_prev), coef2 = sqrt(1 - alpha_bar_prev - sigma^2)
+    const float eps = (c_recip * xt - x0) / c_recipm1;
+    mean = x0 * coef1 + coef2 * eps;
+  } else {
+    mean = coef1 * x0 + coef2 * xt;
+  }
   *x0_out = x0;
   *mean_out = mean;
   return mean + sigma * nz;
@@ -75,7 +83,9 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
   const int step = *a.step_ptr;
   const float coef1 = a.coef[0 * a.n_steps + step];
   const float coef2 = a.coef[1 * a.n_steps + step];
-  const float sigma = (step != 0) ? expf(0.5f * a.coef[2 * a.n_steps + step]) : 0.0f;
+  // row 2: log-variance of the ancestral step, or (ddim) sigma itself
+  const float sigma = (step != 0) ? (a.ddim ? a.coef[2 * a.n_steps + step] : expf(0.5f * a.coef[2 * a.n_steps + step]))
+                                  : 0.0f;
   const float c_recip = a.coef[3 * a.n_steps + step];
   const float c_recipm1 = a.coef[4 * a.n_steps + step];
   const float sc = a.uncond ? a.scale[b] : 1.0f;
@@ -85,6 +95,7 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
   const size_t slab_off = sample_off + (size_t)j0 * T;
   const size_t noise_off = (a.const_noise ? 0 : sample_off) + (size_t)j0 * T;
   const uint64_t rng_sample = a.const_noise ? (uint64_t)a.sample_base : (uint64_t)(a.sample_base + b);
+  const uint64_t rng_seed = a.seed_dev ? *a.seed_dev : a.seed;
   const int n = rows * T;                          // floats in this slab
   const bool vec_ok = ((slab_off & 3) == 0) && ((noise_off & 3) == 0) && ((((size_t)j0 * T) & 3) == 0);
   const int n4 = vec_ok ? (n >> 2) : 0;
@@ -96,7 +107,7 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
     const float4 x = __ldcs(reinterpret_cast<const float4*>(a.x_t + e));
     float4 z;
     if (a.noise) z = __ldcs(reinterpret_cast<const float4*>(a.noise + noise_off + 4 * (size_t)i));
-    else z = philox_normal4((uint32_t)(((size_t)j0 * T >> 2) + i), (uint32_t)step, rng_sample, a.seed);
+    else z = philox_normal4((uint32_t)(((size_t)j0 * T >> 2) + i), (uint32_t)step, rng_sample, rng_seed);
     float4 inp = make_float4(0, 0, 0, 0);
     uchar4 mk = make_uchar4(0, 0, 0, 0);
     if (has_mask) {
@@ -104,10 +115,10 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
       mk = *reinterpret_cast<const uchar4*>(a.inpaint_mask + e);
     }
     float4 x0, mean, o;
-    o.x = post_one(c.x, u.x, sc, has_u, x.x, z.x, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.clip, has_mask, mk.x != 0, inp.x, &x0.x, &mean.x);
-    o.y = post_one(c.y, u.y, sc, has_u, x.y, z.y, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.clip, has_mask, mk.y != 0, inp.y, &x0.y, &mean.y);
-    o.z = post_one(c.z, u.z, sc, has_u, x.z, z.z, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.clip, has_mask, mk.z != 0, inp.z, &x0.z, &mean.z);
-    o.w = post_one(c.w, u.w, sc, has_u, x.w, z.w, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.clip, has_mask, mk.w != 0, inp.w, &x0.w, &mean.w);
+    o.x = post_one(c.x, u.x, sc, has_u, x.x, z.x, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.ddim, a.clip, has_mask, mk.x != 0, inp.x, &x0.x, &mean.x);
+    o.y = post_one(c.y, u.y, sc, has_u, x.y, z.y, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.ddim, a.clip, has_mask, mk.y != 0, inp.y, &x0.y, &mean.y);
+    o.z = post_one(c.z, u.z, sc, has_u, x.z, z.z, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.ddim, a.clip, has_mask, mk.z != 0, inp.z, &x0.z, &mean.z);
+    o.w = post_one(c.w, u.w, sc, has_u, x.w, z.w, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode, a.ddim, a.clip, has_mask, mk.w != 0, inp.w, &x0.w, &mean.w);
     if (a.x_prev) *reinterpret_cast<float4*>(a.x_prev + e) = o;
     if (a.pred_xstart) *reinterpret_cast<float4*>(a.pred_xstart + e) = x0;
     if (a.mean) *reinterpret_cast<float4*>(a.mean + e) = mean;
@@ -130,13 +141,13 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
     if (a.noise) z = a.noise[noise_off + f];
     else {
       const size_t flat = (size_t)j0 * T + f;
-      const float4 z4 = philox_normal4((uint32_t)(flat >> 2), (uint32_t)step, rng_sample, a.seed);
+      const float4 z4 = philox_normal4((uint32_t)(flat >> 2), (uint32_t)step, rng_sample, rng_seed);
       const int l = (int)(flat & 3);
       z = l == 0 ? z4.x : (l == 1 ? z4.y : (l == 2 ? z4.z : z4.w));
     }
     float x0, mean;
     const float o = post_one(c, u, sc, has_u, a.x_t[e], z, coef1, coef2, sigma, c_recip, c_recipm1, a.eps_mode,
-                             a.clip, has_mask, has_mask ? a.inpaint_mask[e] != 0 : false,
+                             a.ddim, a.clip, has_mask, has_mask ? a.inpaint_mask[e] != 0 : false,
                              has_mask ? a.inpainted[e] : 0.f, &x0, &mean);
     if (a.x_prev) a.x_prev[e] = o;
     if (a.pred_xstart) a.pred_xstart[e] = x0;
@@ -292,6 +303,37 @@ extern "C" int gd_pack_rows(const float* src, void* dst, int32_t B, int32_t C, i
   dim3 grid(ceil_div(T, 32), ceil_div(C, 32), B);
   GD_REQUIRE(dst_fmt >= GD_F32 && dst_fmt <= GD_FP16, "gd_pack_rows: bad dst_fmt");
   pack_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, C, T, ld, col_off, dst_fmt);
+  GD_LAUNCH_CHECK();
+  return GD_OK;
+}
+
+namespace gd {
+// One thread per (feature row, frame): out = x * std + mean, routed to the rotation (feature % 6 < 3) or position
+// tensor of the take at frame offset t_off.
+__global__ void unnormalize_split_kernel(const float* __restrict__ x, const float* __restrict__ mean,
+                                         const float* __restrict__ stdv, float* __restrict__ pos,
+                                         float* __restrict__ rot, int J, int T, int t_off, int T_total) {
+  const int f = blockIdx.y, b = blockIdx.z;
+  const int joint = f / 6, c = f - joint * 6;
+  const float m = mean ? mean[f] : 0.f, sd = stdv ? stdv[f] : 1.f;
+  float* dst = (c < 3 ? rot : pos);
+  if (!dst) return;
+  const size_t orow = ((size_t)b * (J / 6) + joint) * 3 + (c < 3 ? c : c - 3);
+  const float* src = x + ((size_t)b * J + f) * T;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < T; t += gridDim.x * blockDim.x)
+    dst[orow * T_total + t_off + t] = __fadd_rn(__fmul_rn(src[t], sd), m);   // two roundings, like data * std + mean
+}
+}  // namespace gd
+
+extern "C" int gd_unnormalize_split(const float* x, const float* mean, const float* stdv, float* pos, float* rot,
+                                    int32_t B, int32_t J, int32_t T, int32_t t_off, int32_t T_total, void* stream) {
+  using namespace gd;
+  GD_REQUIRE(x && (pos || rot), "gd_unnormalize_split: null pointer");
+  GD_REQUIRE(B > 0 && B <= 65535 && J > 0 && J <= 65535 && J % 6 == 0 && T > 0 && t_off >= 0 && t_off + T <= T_total,
+             "gd_unnormalize_split: bad shape B=%d J=%d T=%d t_off=%d T_total=%d (J must be a multiple of 6)", B, J, T,
+             t_off, T_total);
+  dim3 grid(ceil_div(T, 128), J, B);
+  unnormalize_split_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x, mean, stdv, pos, rot, J, T, t_off, T_total);
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

@@ -140,6 +140,22 @@ class GaussianDiffusion:
                 step=th.zeros(1, dtype=th.int32, device=device))
         return self._dev_cache[key]
 
+    def ddim_coef(self, device, eta):
+        """Per-step DDIM coefficients as fp32, computed with the reference's own fp32 operation order on the
+        `.float()`-extracted tables (ddim_sample, gaussian_diffusion.py:765-778): rows sqrt(alpha_bar_prev),
+        sqrt(1 - alpha_bar_prev - sigma^2), sigma = eta*sqrt((1-abp)/(1-ab))*sqrt(1-ab/abp), sqrt_recip,
+        sqrt_recipm1, sigma^2."""
+        key = ("ddim", str(device), float(eta))
+        if key not in self._dev_cache:
+            f = np.float32
+            ab, abp = self.alphas_cumprod.astype(f), self.alphas_cumprod_prev.astype(f)
+            sigma = f(eta) * np.sqrt((f(1) - abp) / (f(1) - ab)) * np.sqrt(f(1) - ab / abp)
+            c_eps = np.sqrt(f(1) - abp - sigma ** 2)
+            rows = [np.sqrt(abp), c_eps, sigma, self.sqrt_recip_alphas_cumprod.astype(f),
+                    self.sqrt_recipm1_alphas_cumprod.astype(f), sigma ** 2]
+            self._dev_cache[key] = th.from_numpy(np.stack(rows).astype(f)).to(device).contiguous()
+        return self._dev_cache[key]
+
     def _scale_timesteps(self, t):
         if self.rescale_timesteps:
             return t.float() * (1000.0 / self.num_timesteps)
@@ -177,7 +193,7 @@ class GaussianDiffusion:
 
     # ------------------------------------------------------------------ fused posterior kernel
     def _posterior(self, model_out, x, t, *, uncond=None, scale=None, noise=None, clip=False, eps_mode=False,
-                   inpaint=None, want="all", const_noise=False):
+                   inpaint=None, want="all", const_noise=False, ddim_eta=None):
         """One launch of gd_posterior_step over [B,J,1,T] tensors (per sample when t is not uniform)."""
         B = x.shape[0]
         per = x[0].numel()
@@ -203,7 +219,9 @@ class GaussianDiffusion:
             nz = None
             if noise is not None:
                 nz = noise if const_noise else noise[sl]
-            K.posterior_step(model_out[sl], x[sl], tabs["coef"], tabs["step"], nb, J, T,
+            K.posterior_step(model_out[sl], x[sl],
+                             tabs["coef"] if ddim_eta is None else self.ddim_coef(x.device, ddim_eta), tabs["step"],
+                             nb, J, T, ddim=ddim_eta is not None,
                              uncond=None if uncond is None else uncond[sl],
                              scale=None if scale is None else scale[sl], noise=nz,
                              x_prev=res["sample"][sl] if "sample" in res else None,
@@ -352,8 +370,87 @@ class GaussianDiffusion:
     def training_losses(self, *a, **k):
         raise NotImplementedError("training is outside the B200 sampling hot path")
 
-    def ddim_sample_loop(self, *a, **k):
-        raise NotImplementedError("DDIM sampling is a 'next' row (SURVEY 8.6), not built yet")
+    # ------------------------------------------------------------------ DDIM (gaussian_diffusion.py:732-993)
+    def ddim_sample(self, model, x, t, clip_denoised=True, denoised_fn=None, cond_fn=None, model_kwargs=None,
+                    eta=0.0):
+        """Sample x_{t-1} with DDIM (:732-782).  The noise is th.randn_like(x), drawn where the reference draws it
+        (:775) even when eta = 0."""
+        if model_kwargs is None:
+            model_kwargs = {}
+        self._check_supported(denoised_fn, cond_fn)
+        model = self._wrap_for_call(model)
+        model_output = model(x, self._scale_timesteps(t), **model_kwargs)
+        noise = th.randn_like(x)
+        return self._ddim_update(model_output, x, t, noise, clip_denoised, model_kwargs, eta)
+
+    def _ddim_update(self, model_output, x, t, noise, clip_denoised, model_kwargs, eta):
+        res = self._posterior(model_output.float().contiguous(), x.float().contiguous(), t,
+                              noise=noise.float().contiguous(), clip=clip_denoised,
+                              eps_mode=self.model_mean_type == ModelMeanType.EPSILON,
+                              inpaint=self._inpaint_of(model_kwargs), ddim_eta=eta)
+        return {"sample": res["sample"], "pred_xstart": res["pred_xstart"]}
+
+    def ddim_sample_loop(self, model, shape, noise=None, clip_denoised=True, denoised_fn=None, cond_fn=None,
+                         model_kwargs=None, device=None, progress=False, eta=0.0, skip_timesteps=0, init_image=None,
+                         randomize_class=False, cond_fn_with_grad=False, dump_steps=None, const_noise=False,
+                         step_noise=None):
+        """Generate samples with DDIM; same contract and the same refusals as the reference (:878-930)."""
+        if dump_steps is not None:
+            raise NotImplementedError()
+        if const_noise == True:  # noqa: E712  (the reference's own test, :902)
+            raise NotImplementedError()
+        final = None
+        for sample in self.ddim_sample_loop_progressive(
+                model, shape, noise=noise, clip_denoised=clip_denoised, denoised_fn=denoised_fn, cond_fn=cond_fn,
+                model_kwargs=model_kwargs, device=device, progress=progress, eta=eta, skip_timesteps=skip_timesteps,
+                init_image=init_image, randomize_class=randomize_class, cond_fn_with_grad=cond_fn_with_grad,
+                step_noise=step_noise, _want_pred=False, _yield_steps=None):
+            if sample is not None:
+                final = sample
+        return final["sample"]
+
+    def ddim_sample_loop_progressive(self, model, shape, noise=None, clip_denoised=True, denoised_fn=None,
+                                     cond_fn=None, model_kwargs=None, device=None, progress=False, eta=0.0,
+                                     skip_timesteps=0, init_image=None, randomize_class=False,
+                                     cond_fn_with_grad=False, step_noise=None, _want_pred=True, _yield_steps="all"):
+        """Yields {'sample','pred_xstart'} per DDIM step (:933-993); engine-backed models replay the captured step
+        graph with the DDIM coefficient table, any other callable goes through `ddim_sample`."""
+        from ..sampler import FastLoop, is_engine_model
+        self._check_supported(denoised_fn, cond_fn)
+        if randomize_class or cond_fn_with_grad:
+            raise NotImplementedError("randomize_class / cond_fn_with_grad are outside the B200 hot path")
+        if model_kwargs is None:
+            model_kwargs = {}
+        if device is None:
+            device = next(model.parameters()).device
+        assert isinstance(shape, (tuple, list))
+        if is_engine_model(model):
+            loop = FastLoop(self, model, device)
+            yield from loop.run(tuple(shape), noise, model_kwargs, clip_denoised, skip_timesteps, init_image,
+                                False, step_noise, progress, _want_pred, _yield_steps, ddim_eta=float(eta))
+            return
+        img = noise if noise is not None else th.randn(*shape, device=device)
+        if skip_timesteps and init_image is None:
+            init_image = th.zeros_like(img)
+        indices = list(range(self.num_timesteps - skip_timesteps))[::-1]
+        if init_image is not None:
+            my_t = th.ones([shape[0]], device=device, dtype=th.long) * indices[0]
+            img = self.q_sample(init_image, my_t, img)
+        if progress:
+            from tqdm.auto import tqdm
+            indices = tqdm(indices)
+        for k, i in enumerate(indices):
+            t = th.tensor([i] * shape[0], device=device)
+            with th.no_grad():
+                if step_noise is not None:
+                    m = self._wrap_for_call(model)
+                    out = self._ddim_update(m(img, self._scale_timesteps(t), **model_kwargs), img, t,
+                                            step_noise[k].to(device), clip_denoised, model_kwargs, eta)
+                else:
+                    out = self.ddim_sample(model, img, t, clip_denoised=clip_denoised, model_kwargs=model_kwargs,
+                                           eta=eta)
+                yield out
+                img = out["sample"]
 
     def plms_sample_loop(self, *a, **k):
         raise NotImplementedError("PLMS sampling is outside the B200 hot path")

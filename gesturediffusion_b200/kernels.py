@@ -180,7 +180,7 @@ def cond_tokens(t, temb_table, seed_emb, pe0, x_f32, x_h16, B, n_branch, S, d, c
 def posterior_step(cond, x_t, coef, step_ptr, B, J, T, uncond=None, scale=None, noise=None, x_prev=None,
                    pred_xstart=None, mean=None, a_next=None, inpaint_mask=None, inpainted=None,
                    timestep_map=None, next_t=None, eps_mode=False, clip=False, const_noise=False, seed=0,
-                   sample_base=0):
+                   sample_base=0, seed_dev=None, ddim=False):
     lib = _cabi.load()
     a = GdPosteriorArgs()
     a.cond, a.uncond, a.scale = _dev(cond, torch.float32, "cond"), _dev(uncond, torch.float32, "uncond"), \
@@ -200,6 +200,8 @@ def posterior_step(cond, x_t, coef, step_ptr, B, J, T, uncond=None, scale=None, 
     a.B, a.J, a.T = B, J, T
     a.eps_mode, a.clip, a.const_noise = int(eps_mode), int(clip), int(const_noise)
     a.seed, a.sample_base = seed, sample_base
+    a.seed_dev = _dev(seed_dev, torch.int64, "seed_dev")
+    a.ddim = int(ddim)
     with _Timed("posterior_step", B=B, J=J, T=T, cfg=uncond is not None, philox=noise is None):
       rc = lib.gd_posterior_step(C.byref(a), _cabi.stream_handle())
     _cabi.check(rc, "gd_posterior_step")
@@ -210,6 +212,19 @@ def pack_rows(src, dst, B, Cc, T, col_off=0):
     rc = lib.gd_pack_rows(_dev(src, torch.float32, "src"), _dev(dst, None, "dst"), B, Cc, T, dst.stride(0), col_off,
                           fmt_of(dst), _cabi.stream_handle())
     _cabi.check(rc, "gd_pack_rows")
+
+
+def unnormalize_split(x, mean, std, pos, rot, t_off):
+    """x [B, J, T] (or [B, J, 1, T]) fp32 -> pos / rot [B, J/6, 3, T_total] at frame offset t_off (generate.py:132-146)."""
+    lib = _cabi.load()
+    B, J, T = x.shape[0], x.shape[1], x.shape[-1]
+    ref = pos if pos is not None else rot
+    rc = lib.gd_unnormalize_split(_dev(x, torch.float32, "x"), _dev(mean, torch.float32, "mean") if mean is not None else None,
+                                  _dev(std, torch.float32, "std") if std is not None else None,
+                                  _dev(pos, torch.float32, "pos") if pos is not None else None,
+                                  _dev(rot, torch.float32, "rot") if rot is not None else None,
+                                  B, J, T, t_off, ref.shape[-1], _cabi.stream_handle())
+    _cabi.check(rc, "gd_unnormalize_split")
 
 
 def q_sample(x0, noise, sqrt_acp, sqrt_1macp, step, out):

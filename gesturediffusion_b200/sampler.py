@@ -46,7 +46,8 @@ class FastLoop:
             B, J, T = ws["B"], self.engine.J, ws["T"]
             dev = self.device
             st = dict(x=torch.zeros(B, J, T, device=dev), scale=torch.ones(B, device=dev),
-                      step=torch.zeros(1, dtype=torch.int32, device=dev), graphs={})
+                      step=torch.zeros(1, dtype=torch.int32, device=dev),
+                      seed=torch.zeros(1, dtype=torch.int64, device=dev), graphs={})
             if want_pred:
                 st["pred"] = torch.zeros(B, J, T, device=dev)
             if has_noise_buf:
@@ -57,23 +58,24 @@ class FastLoop:
             ws[key] = st
         return st
 
-    def _step(self, ws, st, tabs, flags):
+    def _step(self, ws, st, tabs, flags, coef):
         """One denoising step: model evaluation + fused update (in place on st['x'])."""
         eng, d = self.engine, self.diffusion
         B, J, T = ws["B"], eng.J, ws["T"]
         eng.forward_step(ws)
         out = ws["OUT"]
-        K.posterior_step(out[:B], st["x"], tabs["coef"], st["step"], B, J, T,
+        K.posterior_step(out[:B], st["x"], coef, st["step"], B, J, T,
                          uncond=out[B:] if self.cfg else None, scale=st["scale"] if self.cfg else None,
                          noise=st.get("noise"), x_prev=st["x"], pred_xstart=st.get("pred"),
                          a_next=ws["a_in"], inpaint_mask=st.get("mask"), inpainted=st.get("motion"),
                          timestep_map=tabs["timestep_map"], next_t=ws["t"],
                          eps_mode=d.model_mean_type == ModelMeanType.EPSILON, clip=flags["clip"],
-                         const_noise=flags["const_noise"], seed=d.seed, sample_base=d.sample_base)
+                         const_noise=flags["const_noise"], seed=d.seed, sample_base=d.sample_base,
+                         seed_dev=st["seed"], ddim=flags["ddim"])
 
     # -------------------------------------------------------------- the loop
     def run(self, shape, noise, model_kwargs, clip_denoised, skip_timesteps, init_image, const_noise, step_noise,
-            progress, want_pred, yield_steps):
+            progress, want_pred, yield_steps, ddim_eta=None):
         d, eng = self.diffusion, self.engine
         dev = self.device
         B, J, F_, T = shape
@@ -108,7 +110,7 @@ class FastLoop:
                 img = noise.to(dev, torch.float32).reshape(B, eng.J, T).contiguous()
             elif rng == "philox":
                 img = torch.empty(B, eng.J, T, device=dev)
-                K.philox_normal(img, B, eng.J, T, d.seed, d.sample_base, d.num_timesteps)
+                K.philox_normal(img, B, eng.J, T, int(d.seed) & 0x7FFFFFFFFFFFFFFF, d.sample_base, d.num_timesteps)
             else:
                 img = torch.randn(*shape, device=dev).reshape(B, eng.J, T)
             if skip_timesteps and init_image is None:
@@ -120,8 +122,12 @@ class FastLoop:
                            tabs["sqrt_acp"], tabs["sqrt_1macp"], first, q)
                 img = q
 
-            flags = dict(clip=bool(clip_denoised), const_noise=bool(const_noise))
-            gkey = (flags["clip"], flags["const_noise"], d.model_mean_type, d.seed, d.sample_base, id(tabs["coef"]))
+            # DDIM (ddim_sample_loop_progressive, :933-993) replays the same step with another coefficient table
+            coef = tabs["coef"] if ddim_eta is None else d.ddim_coef(dev, ddim_eta)
+            flags = dict(clip=bool(clip_denoised), const_noise=bool(const_noise), ddim=ddim_eta is not None)
+            # the Philox seed is read from device memory, so one captured graph serves every seed (chunked takes)
+            st["seed"].fill_(int(d.seed) & 0x7FFFFFFFFFFFFFFF)
+            gkey = (flags["clip"], flags["const_noise"], d.model_mean_type, d.sample_base, flags["ddim"], id(coef))
             graph = None
             if d.use_cuda_graph:
                 graph = st["graphs"].get(gkey)
@@ -130,11 +136,11 @@ class FastLoop:
                     st["x"].copy_(img)
                     eng.load_x(ws, st["x"])
                     K.set_loop_state(st["step"], ws["t"], tabs["timestep_map"], first, B)
-                    self._step(ws, st, tabs, flags)
+                    self._step(ws, st, tabs, flags, coef)
                     torch.cuda.current_stream().synchronize()
                     graph = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(graph):
-                        self._step(ws, st, tabs, flags)
+                        self._step(ws, st, tabs, flags, coef)
                     st["graphs"][gkey] = graph
 
             st["x"].copy_(img)
@@ -155,7 +161,7 @@ class FastLoop:
                     STATS["graph_replays"] += 1
                     STATS["graph_kernels"] += self.launches_per_step()
                 else:
-                    self._step(ws, st, tabs, flags)
+                    self._step(ws, st, tabs, flags, coef)
                 last = k == n_exec - 1
                 if yield_steps == "all" or last or (yield_steps is not None and k in yield_steps):
                     out = {"sample": st["x"].view(B, J, F_, T).clone()}

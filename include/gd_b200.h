@@ -157,6 +157,9 @@ typedef struct gdPosteriorArgs {
   int32_t B, J, T;
   int32_t eps_mode, clip, const_noise;
   uint64_t seed; int64_t sample_base;
+  const uint64_t* seed_dev;   /* optional: Philox seed read from device memory (one captured graph, many calls) */
+  int32_t ddim;               /* 1: DDIM update (gaussian_diffusion.py:732-782): coef rows 0/1/2 hold
+                                 sqrt(alpha_bar_prev), sqrt(1 - alpha_bar_prev - sigma^2), sigma(eta) per step */
 } gdPosteriorArgs;
 int gd_posterior_step(const gdPosteriorArgs* args, void* stream);
 
@@ -164,6 +167,15 @@ int gd_posterior_step(const gdPosteriorArgs* args, void* stream);
  * src [B, C, T] fp32 -> dst[(b*T + t) * ld + col_off + c] (dst_fmt: GD_F32 / GD_BF16 / GD_FP16). */
 int gd_pack_rows(const float* src, void* dst, int32_t B, int32_t C, int32_t T, int32_t ld,
                  int32_t col_off, int32_t dst_fmt, void* stream);
+
+/* Post-processing of one generated chunk (sample/generate.py:132-146 with data_loaders/gesture/data/dataset.py:
+ * 118-119): inverse normalisation x * std + mean per feature, then the 6-interleaved GENEA layout
+ * [rot_x, rot_y, rot_z, pos_x, pos_y, pos_z] per joint is split into
+ *   rot[b][joint][c][t_off + t] and pos[b][joint][c][t_off + t]   ([B, J/6, 3, T_total] fp32, either may be NULL),
+ * i.e. the reference's permuted [B, n_joints, 3, chunk_len] tensors written straight into the take at the chunk's
+ * frame offset.  x is [B, J, T] fp32 (= [B, J, 1, T]); mean / std are [J] or NULL (0 / 1). */
+int gd_unnormalize_split(const float* x, const float* mean, const float* stdv, float* pos, float* rot, int32_t B,
+                         int32_t J, int32_t T, int32_t t_off, int32_t T_total, void* stream);
 
 /* q_sample (gaussian_diffusion.py:233-251) for skip_timesteps/init_image:
  * out = a[step]*x0 + b[step]*noise with a/b fp32 device tables. */

@@ -205,6 +205,41 @@ class OracleDiffusion:
         return img
 
 
+    # ------------------------------------------------------------------ DDIM
+    def ddim_sample(self, model_fn, x, t, y, noise, clip_denoised=True, eta=0.0):
+        """gaussian_diffusion.py:732-782 (cond_fn = None): eps re-derived from pred_xstart (:763, :283-289),
+        sigma (:767-771), eq. 12 (:774-782); fp32 tensor arithmetic in the reference's operation order."""
+        pmv = self.p_mean_variance(model_fn, x, t, y, clip_denoised)
+        x0 = pmv["pred_xstart"]
+        eps = ((self._pick("sqrt_recip_alphas_cumprod", t, x) * x - x0)
+               / self._pick("sqrt_recipm1_alphas_cumprod", t, x))
+        ab = self._pick("alphas_cumprod", t, x)
+        abp = self._pick("alphas_cumprod_prev", t, x)
+        sigma = eta * torch.sqrt((1 - abp) / (1 - ab)) * torch.sqrt(1 - ab / abp)
+        mean = x0 * torch.sqrt(abp) + torch.sqrt(1 - abp - sigma ** 2) * eps
+        keep = (t != 0).float().view(-1, *([1] * (x.dim() - 1)))
+        return dict(sample=mean + keep * sigma * noise, pred_xstart=x0)
+
+    def ddim_sample_loop(self, model_fn, x_T, y, step_noise, clip_denoised=True, eta=0.0,
+                         skip_timesteps=0, init_image=None, trace=None):
+        """gaussian_diffusion.py:933-993; step_noise[k] is what th.randn_like (:775) returns at the k-th step."""
+        img = x_T
+        B = x_T.shape[0]
+        if skip_timesteps and init_image is None:
+            init_image = torch.zeros_like(img)
+        order = list(range(self.num_timesteps - skip_timesteps))[::-1]
+        if init_image is not None:
+            t0 = torch.full((B,), order[0], dtype=torch.long)
+            img = self.q_sample(init_image, t0, img)
+        for k, i in enumerate(order):
+            t = torch.full((B,), i, dtype=torch.long)
+            out = self.ddim_sample(model_fn, img, t, y, step_noise[k], clip_denoised, eta)
+            if trace is not None:
+                trace.append(dict(t=i, x_t=img, pred_xstart=out["pred_xstart"], sample=out["sample"]))
+            img = out["sample"]
+        return img
+
+
 def oracle_cfg(model_fn):
     """cfg_sampler.py:23-28: uncond + scale*(cond-uncond); model_fn(x,t,y,uncond=bool)."""
     def guided(x, t, y):

@@ -129,8 +129,77 @@ def chain_fixtures():
         print("%s.npz" % name, "steps", len(trace))
 
 
+# name -> (model case, respacing, cfg?, eta, clip_denoised)
+DDIM_CASES = {
+    "ddim_v1_small_cfg6_eta0": ("v1_small", "ddim6", True, 0.0, True),
+    "ddim_v2_small_cfg5_eta05": ("v2_small", "ddim5", True, 0.5, False),
+    "ddim_v2_small_uncond8_eta1": ("v2_small", [8], False, 1.0, True),
+}
+# name -> (model case, respacing, chunks, guidance)
+TAKE_CASES = {"take_v2_small_cfg4x3": ("v2_small", [4], 3, 2.5), "take_v1_small_cfg3x2": ("v1_small", [3], 2, 2.5)}
+
+
+def ddim_fixtures():
+    """ddim_sample_loop_progressive of the reference (gaussian_diffusion.py:933-993) with injected noise."""
+    ns = ref_shims.load_reference()
+    for name, (case, resp, use_cfg, eta, clip) in DDIM_CASES.items():
+        cfg, sd, m, x, y = build(case)
+        dif = ref_shims.build_reference_diffusion(resp)
+        model = ns.ClassifierFreeSampleModel(m) if use_cfg else m
+        noises = make_step_noise(tuple(x.shape), dif.num_timesteps)
+        trace = []
+        with ref_shims.injected_noise(noises):
+            for out in dif.ddim_sample_loop_progressive(model, tuple(x.shape), noise=x, clip_denoised=clip,
+                                                        model_kwargs={"y": dict(y)}, eta=eta):
+                trace.append((out["sample"].clone(), out["pred_xstart"].clone()))
+        np.savez(os.path.join(OUT, "%s.npz" % name), final=trace[-1][0].numpy(),
+                 trace_sample=np.stack([t[0].numpy() for t in trace]),
+                 trace_pred=np.stack([t[1].numpy() for t in trace]),
+                 meta=json.dumps(dict(case=case, respacing=resp, cfg=use_cfg, eta=eta, clip=clip,
+                                      n_exec=dif.num_timesteps)))
+        print("%s.npz" % name, "steps", len(trace))
+
+
+def take_inputs(cfg, B, T, chunks):
+    """Per-chunk conditioning, chunk-specific noise and dataset statistics of a synthetic take."""
+    ys = [make_inputs(cfg, B, T, seed=500 + k)[1] for k in range(chunks)]
+    x_T = [make_inputs(cfg, B, T, seed=600 + k)[0] for k in range(chunks)]
+    g = torch.Generator().manual_seed(77)
+    mean = torch.randn(cfg["njoints"], generator=g)
+    std = torch.rand(cfg["njoints"], generator=g) + 0.5
+    return ys, x_T, mean, std
+
+
+def take_fixtures():
+    """The chunk loop of sample/generate.py:91-189 run on the reference model / diffusion objects (the script's
+    own data loading, argument parsing and rendering are not part of the path)."""
+    from oracle.generate_oracle import oracle_generate_take
+    ns = ref_shims.load_reference()
+    for name, (case, resp, chunks, guidance) in TAKE_CASES.items():
+        cfg, sd, m, x, _ = build(case)
+        B, T = x.shape[0], x.shape[-1]
+        dif = ref_shims.build_reference_diffusion(resp)
+        model = ns.ClassifierFreeSampleModel(m)
+        ys, x_T, mean, std = take_inputs(cfg, B, T, chunks)
+
+        def sample_fn(y, k):
+            noises = make_step_noise(tuple(x.shape), dif.num_timesteps, seed=4321 + k)
+            with ref_shims.injected_noise(noises):
+                return dif.p_sample_loop(model, (B, m.njoints, m.nfeats, T), clip_denoised=False,
+                                         model_kwargs={"y": y}, skip_timesteps=0, init_image=None, progress=False,
+                                         dump_steps=None, noise=x_T[k], const_noise=False)
+        out = oracle_generate_take(sample_fn, ys, B, cfg["seed_poses"], guidance, mean, std)
+        np.savez(os.path.join(OUT, "%s.npz" % name), sample=out["sample"].numpy(), motion=out["motion"],
+                 motion_rot=out["motion_rot"],
+                 meta=json.dumps(dict(case=case, respacing=resp, chunks=chunks, guidance=guidance,
+                                      n_exec=dif.num_timesteps)))
+        print("%s.npz" % name, out["motion"].shape)
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     schedule_fixture()
     model_fixtures()
     chain_fixtures()
+    ddim_fixtures()
+    take_fixtures()

@@ -60,3 +60,38 @@ def build_product_model(cfg, sd, device, precision):
 
 def to_dev(y, device):
     return {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in y.items()}
+
+
+DDIM_CASES = ["ddim_v1_small_cfg6_eta0", "ddim_v2_small_cfg5_eta05", "ddim_v2_small_uncond8_eta1"]
+TAKE_CASES = ["take_v2_small_cfg4x3", "take_v1_small_cfg3x2"]
+
+
+def load_ddim_case(name):
+    g = np.load(os.path.join(GOLDEN, "%s.npz" % name))
+    meta = json.loads(str(g["meta"]))
+    cfg, sd, x, y, _ = load_model_case(meta["case"])
+    noises = make_step_noise(tuple(x.shape), meta["n_exec"])
+    gold = dict(final=torch.from_numpy(g["final"]), trace_sample=torch.from_numpy(g["trace_sample"]),
+                trace_pred=torch.from_numpy(g["trace_pred"]))
+    return cfg, sd, x, y, noises, meta, gold
+
+
+def take_inputs(cfg, B, T, chunks):
+    """Same construction as tests/golden/make_golden.py::take_inputs."""
+    ys = [make_inputs(cfg, B, T, seed=500 + k)[1] for k in range(chunks)]
+    x_T = [make_inputs(cfg, B, T, seed=600 + k)[0] for k in range(chunks)]
+    g = torch.Generator().manual_seed(77)
+    mean = torch.randn(cfg["njoints"], generator=g)
+    std = torch.rand(cfg["njoints"], generator=g) + 0.5
+    return ys, x_T, mean, std
+
+
+def load_take_case(name):
+    g = np.load(os.path.join(GOLDEN, "%s.npz" % name))
+    meta = json.loads(str(g["meta"]))
+    cfg, sd, x, _, _ = load_model_case(meta["case"])
+    B, T = x.shape[0], x.shape[-1]
+    ys, x_T, mean, std = take_inputs(cfg, B, T, meta["chunks"])
+    step_noise = [make_step_noise(tuple(x.shape), meta["n_exec"], seed=4321 + k) for k in range(meta["chunks"])]
+    gold = {k: torch.from_numpy(g[k]) for k in ("sample", "motion", "motion_rot")}
+    return cfg, sd, B, T, ys, x_T, mean, std, step_noise, meta, gold
