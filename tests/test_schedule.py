@@ -54,6 +54,10 @@ def test_out_of_scope_paths_raise():
     with pytest.raises(NotImplementedError):
         d.training_losses(None, None, None)
     with pytest.raises(NotImplementedError):
-        d.ddim_sample_loop(None, (1, 2, 1, 10))
+        d.plms_sample_loop(None, (1, 2, 1, 10))
+    with pytest.raises(NotImplementedError):                       # the reference's own refusals (:900-903)
+        d.ddim_sample_loop(None, (1, 2, 1, 10), dump_steps=[0])
+    with pytest.raises(NotImplementedError):
+        d.ddim_sample_loop(None, (1, 2, 1, 10), const_noise=True)
     with pytest.raises(NotImplementedError):
         d._check_supported(denoised_fn=lambda x: x)
