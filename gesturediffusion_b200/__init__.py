@@ -7,6 +7,9 @@ a drop-in behind the reference's Python API for that path:
     diffusion.gaussian_diffusion (gd.*)        ->  gesturediffusion_b200.diffusion.gaussian_diffusion
     model.mdm.MDM / model.mdm_old.MDM_Old      ->  gesturediffusion_b200.model.mdm.MDM / .mdm_old.MDM_Old
     model.cfg_sampler.ClassifierFreeSampleModel->  gesturediffusion_b200.model.cfg_sampler.ClassifierFreeSampleModel
+    utils.model_util (loader path)             ->  gesturediffusion_b200.utils.model_util
+    data_loaders.tensors.gg_collate            ->  gesturediffusion_b200.data_loaders.tensors.gg_collate
+    the chunk loop of sample/generate.py       ->  gesturediffusion_b200.generate.generate_take
 
 Host code is Python/PyTorch (device memory, streams, torch.distributed); all arithmetic of the path
 runs in hand-written CUDA kernels behind the C ABI in include/gd_b200.h.  No CPU fallback.

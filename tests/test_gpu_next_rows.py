@@ -114,3 +114,47 @@ def test_unnormalize_split_kernel(cuda_device):
     from gesturediffusion_b200 import _cabi
     with pytest.raises(_cabi.GdError, match="multiple of 6"):
         K.unnormalize_split(torch.zeros(1, 7, 4, device=cuda_device), None, None, torch.zeros(1, 1, 3, 4, device=cuda_device), None, 0)
+
+
+def test_checkpoint_to_take_end_to_end(cuda_device, tmp_path):
+    """args.json + checkpoint -> load_checkpoint -> gg_collate'd chunks -> generate_take (sample/generate.py:62-189
+    through the package), checked chunk by chunk against separate p_sample_loop calls + the oracle post-processing."""
+    import json
+    import os
+    import numpy as np
+    from gesturediffusion_b200.data_loaders.tensors import gg_collate
+    from gesturediffusion_b200.generate import generate_take
+    from gesturediffusion_b200.synthetic import make_state_dict, make_step_noise, model_config
+    from gesturediffusion_b200.utils import model_util
+    from oracle.generate_oracle import oracle_split_positions_rotations
+    cfg = model_config(arch="v2", njoints=498, latent_dim=128, num_layers=2, num_heads=4, ff_size=1024)
+    path = os.path.join(str(tmp_path), "model.pt")
+    torch.save(make_state_dict(cfg, seed=3), path)
+    with open(os.path.join(str(tmp_path), "args.json"), "w") as fh:
+        json.dump(dict(dataset="genea2023", layers=2, latent_dim=128, cond_mask_prob=0.1, use_text=False,
+                       use_audio=False, mfcc_input=True, use_wav_enc=False, seed_poses=10, noise_schedule="cosine",
+                       sigma_small=True, lambda_vel=0.0, lambda_rcxyz=0.0, lambda_fc=0.0), fh)
+    model, dif, args = model_util.load_checkpoint(path, device=cuda_device, precision="fp32", timestep_respacing=[4])
+    B, T, chunks = 2, 120, 2
+    r = np.random.RandomState(1)
+    conds = [gg_collate([(r.randn(T, 498), "w", T, r.randn(800), r.randn(T, 26), r.randn(10, 498))
+                         for _ in range(B)])[1]["y"] for _ in range(chunks)]
+    g = torch.Generator().manual_seed(2)
+    mean, std = torch.randn(498, generator=g), torch.rand(498, generator=g) + 0.5
+    x_T = [torch.randn(B, 498, 1, T, generator=g) for _ in range(chunks)]
+    noises = [make_step_noise((B, 498, 1, T), 4, seed=50 + k) for k in range(chunks)]
+    out = generate_take(model, dif, conds, B, T, guidance_param=args.guidance_param, mean=mean, std=std,
+                        init_noise=[v.to(cuda_device) for v in x_T], step_noise=noises)
+    assert tuple(out["motion"].shape) == (B, 83, 3, chunks * T) and bool(torch.isfinite(out["motion"]).all())
+    prev = None
+    for k in range(chunks):
+        y = to_dev({kk: v for kk, v in conds[k].items()}, cuda_device)
+        if k:
+            y["seed"] = prev[..., -10:]
+        y["scale"] = torch.ones(B, device=cuda_device) * args.guidance_param
+        prev = dif.p_sample_loop(model, (B, 498, 1, T), clip_denoised=False, model_kwargs={"y": y},
+                                 noise=x_T[k].to(cuda_device), step_noise=noises[k])
+        assert torch.equal(prev, out["sample"][..., k * T:(k + 1) * T])
+        pos, rot = oracle_split_positions_rotations(prev, mean, std)
+        assert torch.equal(out["motion"][..., k * T:(k + 1) * T].cpu(), pos.contiguous())
+        assert torch.equal(out["motion_rot"][..., k * T:(k + 1) * T].cpu(), rot.contiguous())
