@@ -57,8 +57,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const int S = p.S, Sp = p.Sp, n_qt = p.n_qt;
   const int kv_bytes = Sp * 256;                            // one K (or V): 2 slabs of [Sp rows x 128 B]
   const int slab = Sp * 128;
-  const int n_local = (p.n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-  const int U = n_local * n_qt;
+  // Items are dealt round-robin; when the last, partial round leaves at most half of the CTAs busy (512 items on 148
+  // CTAs: 68), its items are split into their two query tiles ("solo" units with their own K/V load) so that round
+  // costs half an item: 3.5 instead of 4 item times.
+  const int G = (int)gridDim.x, cta = (int)blockIdx.x;
+  const int full = p.n_items / G, rem = p.n_items - full * G;
+  const bool split_tail = n_qt == 2 && rem > 0 && 2 * rem <= G;
+  const int n_whole = full + ((!split_tail && cta < rem) ? 1 : 0);      // items this CTA processes whole
+  const int U_whole = n_whole * n_qt;
+  const int U = U_whole + ((split_tail && cta < 2 * rem) ? 1 : 0);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_q);
@@ -83,9 +90,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   ptx::grid_dep_launch();
 
   // unit u -> (item, query tile, kv buffer); both kv-buffer use counts equal u >> 1
-  auto item_of = [&](int u) { return (int)blockIdx.x + (n_qt == 2 ? (u >> 1) : u) * (int)gridDim.x; };
-  auto qt_of = [&](int u) { return n_qt == 2 ? (u & 1) : 0; };
+  // (a solo unit has an even index, so slot / use / buffer bookkeeping is the same as for a first tile)
+  auto item_of = [&](int u) { return u < U_whole ? cta + (n_qt == 2 ? (u >> 1) : u) * G : full * G + (cta >> 1); };
+  auto qt_of = [&](int u) { return u < U_whole ? (n_qt == 2 ? (u & 1) : 0) : (cta & 1); };
   auto kvb_of = [&](int u) { return n_qt == 2 ? 0 : (u & 1); };
+  auto first_of = [&](int u) { return u >= U_whole || qt_of(u) == 0; };            // first / last unit using the
+  auto last_of = [&](int u) { return u >= U_whole || qt_of(u) == n_qt - 1; };      // item's K and V
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -100,7 +110,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         uint8_t* qs = q_smem + slot * kAtQBytes;
         ptx::tma_load_2d(qs, &tmap_q, &q_full[slot], colq, row0 + qt * 128);
         ptx::tma_load_2d(qs + 16384, &tmap_q, &q_full[slot], colq + 64, row0 + qt * 128);
-        if (qt == n_qt - 1) {                               // after the item's last Q tile: its K and V
+        if (last_of(u)) {                                   // after the item's last Q tile: its K and V
           uint8_t* ks = kv_smem + b * 2 * kv_bytes;
           uint8_t* vs = ks + kv_bytes;
           ptx::mbar_wait(&k_empty[b], (use & 1) ^ 1);
@@ -124,7 +134,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const int slot = u & 1, use = u >> 1, qt = qt_of(u), b = kvb_of(u);
           ptx::mbar_wait(&slot_free[slot], (use & 1) ^ 1);
           ptx::mbar_wait(&q_full[slot], use & 1);
-          if (qt == 0) ptx::mbar_wait(&k_full[b], use & 1);
+          if (first_of(u)) ptx::mbar_wait(&k_full[b], use & 1);
           ptx::tc_fence_after();
           const uint32_t qa = ptx::smem_u32(q_smem + slot * kAtQBytes);
           const uint32_t ka = ptx::smem_u32(kv_smem + b * 2 * kv_bytes);
@@ -137,14 +147,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           }
           ptx::umma_commit(&s_full[slot]);
           ptx::umma_commit(&q_empty[slot]);
-          if (qt == n_qt - 1) ptx::umma_commit(&k_empty[b]);
+          if (last_of(u)) ptx::umma_commit(&k_empty[b]);
         }
         for (int e = 0; e < 2; ++e) {                       // O = P V for the pair
           const int u = u0 + e;
           if (u >= U) break;
           const int slot = u & 1, use = u >> 1, qt = qt_of(u), b = kvb_of(u);
           ptx::mbar_wait(&p_ready[slot], use & 1);
-          if (qt == 0) ptx::mbar_wait(&v_full[b], use & 1);
+          if (first_of(u)) ptx::mbar_wait(&v_full[b], use & 1);
           ptx::tc_fence_after();
           const uint32_t va = ptx::smem_u32(kv_smem + b * 2 * kv_bytes + kv_bytes);
           const uint32_t tp = tmem_base + (uint32_t)(slot * 256);
@@ -155,7 +165,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             ptx::umma_h16_ts(to, tp + (uint32_t)(k * 8), db, p.idesc_o, k != 0 ? 1u : 0u);
           }
           ptx::umma_commit(&o_full[slot]);
-          if (qt == n_qt - 1) ptx::umma_commit(&v_empty[b]);
+          if (last_of(u)) ptx::umma_commit(&v_empty[b]);
         }
       }
     }
@@ -325,7 +335,9 @@ int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_head
   p.idesc_o = ptx::umma_idesc_h16_f32_bmn(128, 128, fmt == GD_FP16);
   const int sms = num_sms();
   GD_REQUIRE(sms > 0, "gd_attention_h16: cannot query the SM count");
-  const int grid = p.n_items < sms ? p.n_items : sms;
+  // few items (small batches): one CTA per query tile instead of per item when that fits (the kernel's tail split)
+  int grid = p.n_items < sms ? p.n_items : sms;
+  if (p.n_qt == 2 && 2 * p.n_items <= sms) grid = 2 * p.n_items;
   GD_CUDA_OK(launch_pdl(attention_tc_kernel, dim3(grid), dim3(kAtThreads), kAtSmemBytes, stream, tq, tkv, p));
   GD_LAUNCH_CHECK();
   return GD_OK;
