@@ -145,7 +145,10 @@ def test_gemm_epilogue_rowmap_dup_tables_transposed(cuda_device, dtype):
                                          # tcgen05 kernel (dh 128, S <= 256): edge lengths, one and two query tiles,
                                          # and enough (sequence, head) items for several units per CTA
                                          (1, 1, 1, 128), (3, 16, 2, 128), (2, 128, 4, 128), (2, 129, 4, 128),
-                                         (1, 256, 4, 128), (5, 61, 3, 128), (160, 121, 4, 128), (100, 197, 4, 128)])
+                                         (1, 256, 4, 128), (5, 61, 3, 128), (160, 121, 4, 128), (100, 197, 4, 128),
+                                         # two query tiles: split last round (512 items on 148 CTAs), all-solo small batch
+                                         # (68 items -> 136 CTAs), exact rounds (148 items), odd item count
+                                         (128, 197, 4, 128), (17, 197, 4, 128), (37, 200, 4, 128), (51, 197, 3, 128)])
 @pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
 def test_attention(cuda_device, n_seq, S, H, dh, dtype):
     Kn = _K()
@@ -205,6 +208,39 @@ def test_gemm_ln_fused(cuda_device, M, N, K, dtype):
     o32 = torch.empty_like(res)
     Kn.gemm_ln(a, w, bias, res, gamma, beta, out_f32=o32)
     assert torch.equal(o32, x32)
+
+
+def test_gemm_ln_repeatable_under_load(cuda_device):
+    """The cluster exchange (st.async + transaction bytes), the residual ring and the aliased staging blocks carry
+    no race: 24 back-to-back launches at the bench shape (3 tiles per cluster, ragged last tile absent / present),
+    for both operand-stage variants, give the same bits every time, only-16-bit and only-fp32 outputs included."""
+    Kn = _K()
+    for M, Kd in ((25216, 512), (25216 - 37, 1024)):
+        g = torch.Generator(device="cuda").manual_seed(M)
+        a = torch.randn(M, Kd, device="cuda", generator=g).half()
+        w = (torch.randn(512, Kd, device="cuda", generator=g) / math.sqrt(Kd)).half()
+        bias, gamma, beta = (torch.randn(512, device="cuda", generator=g) for _ in range(3))
+        res = torch.randn(M, 512, device="cuda", generator=g)
+        first32 = first16 = None
+        for it in range(24):
+            o32 = torch.full((M, 512), float("nan"), device="cuda")
+            o16 = torch.zeros(M, 512, device="cuda", dtype=torch.float16)
+            if it % 3 == 0:
+                Kn.gemm_ln(a, w, bias, res, gamma, beta, out_f32=o32, out_h16=o16)
+            elif it % 3 == 1:
+                Kn.gemm_ln(a, w, bias, res, gamma, beta, out_f32=o32)
+                o16 = o32.half()
+            else:
+                Kn.gemm_ln(a, w, bias, res, gamma, beta, out_h16=o16)
+                o32 = None
+            if first32 is None:
+                first32, first16 = o32, o16
+                y = res.double() + a.double() @ w.double().t() + bias.double()
+                ref = torch.nn.functional.layer_norm(y, (512,), gamma.double(), beta.double(), 1e-5)
+                assert rel_l2(o32, ref) < 5e-6
+            else:
+                assert o32 is None or torch.equal(o32, first32)
+                assert torch.equal(o16, first16)
 
 
 def test_gemm_ln_rejects_other_widths(cuda_device):
