@@ -338,7 +338,7 @@ int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_head
   // few items (small batches): one CTA per query tile instead of per item when that fits (the kernel's tail split)
   int grid = p.n_items < sms ? p.n_items : sms;
   if (p.n_qt == 2 && 2 * p.n_items <= sms) grid = 2 * p.n_items;
-  GD_CUDA_OK(launch_pdl(attention_tc_kernel, dim3(grid), dim3(kAtThreads), kAtSmemBytes, stream, tq, tkv, p));
+  GD_CUDA_OK(launch_pdl(PDL_ATTENTION, attention_tc_kernel, dim3(grid), dim3(kAtThreads), kAtSmemBytes, stream, tq, tkv, p));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

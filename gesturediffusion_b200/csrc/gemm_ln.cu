@@ -401,7 +401,7 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
   const int m_tiles = ceil_div(p.M, kLnBM);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  GD_CUDA_OK(launch_pdl(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS>, dim3(2 * clusters), dim3(kLnThreads), Cfg::kSmemBytes,
+  GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS>, dim3(2 * clusters), dim3(kLnThreads), Cfg::kSmemBytes,
                         stream, ta, tw, tr, to32, to16, p));
   GD_LAUNCH_CHECK();
   return GD_OK;

@@ -629,7 +629,7 @@ static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, in
   const int workers = tiles < g_num_sms / CG ? tiles : g_num_sms / CG;
   const uint32_t idesc = ptx::umma_idesc_h16_f32(kBM * CG, BN, fmt == GD_FP16);
   if (CG == 1) {
-    GD_CUDA_OK(launch_pdl(gemm_h16_tcgen05_kernel<BN, EPI, CG>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
+    GD_CUDA_OK(launch_pdl(PDL_GEMM, gemm_h16_tcgen05_kernel<BN, EPI, CG>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
                           ta, tw, to, M, N, K, idesc, *ep, gemm_dbg()));
   } else {
     cudaLaunchConfig_t cfg = {};
