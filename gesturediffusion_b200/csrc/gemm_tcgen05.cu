@@ -269,18 +269,40 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
         // Every linear gdEpilogue feature (bias, row table, per-sequence bias, residual, row map, copies; no
         // activation, no out_t) on row-contiguous quads: TMEM -> registers (row = lane) -> this warp's swizzled
         // staging block -> lane (it, c4) takes columns 4*c4 .. 4*c4+3 of row 4*it + lane/8, so table, residual and
-        // output accesses are full 128-byte lines.  The row index arithmetic (three integer divisions) is done once
-        // per tile by the lane that owns the row in TMEM and handed to the quad's lane with a shuffle.
+        // output accesses are full 128-byte lines.
         const int c4 = lane & 7, rsub = lane >> 3;
-        int tabrow_l, outrow_l, seqrow_l;                    // of row `lane`; fetched per quad with a shuffle
+        int tabrow[8], outrow[8], seqrow[8];                 // of this lane's eight quad rows (4*it + lane/8)
         {
-          const int mm = m_warp + lane;
-          tabrow_l = ep.rowtab ? (mm % ep.tab_period) + ep.tab_offset : 0;
-          seqrow_l = ep.seqbias ? mm / ep.seq_rows : 0;
+          const int mm = m_warp + lane;                      // computed for row `lane`, handed over by shuffle
+          const int tabrow_l = ep.rowtab ? (mm % ep.tab_period) + ep.tab_offset : 0;
+          const int seqrow_l = ep.seqbias ? mm / ep.seq_rows : 0;
           const int mapped = ep.map_t > 0 ? (mm / ep.map_t) * ep.map_s + ep.map_off + (mm % ep.map_t) : mm;
-          outrow_l = mm < M ? mapped : -1;
+          const int outrow_l = mm < M ? mapped : -1;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rl = it * 4 + rsub;
+            tabrow[it] = __shfl_sync(0xffffffffu, tabrow_l, rl);
+            seqrow[it] = __shfl_sync(0xffffffffu, seqrow_l, rl);
+            outrow[it] = __shfl_sync(0xffffffffu, outrow_l, rl);
+          }
         }
         const int ncopy = ep.dup > 1 ? ep.dup : 1;
+        // bias + the row-table quads of a chunk (HBM latency when the table is per row, as in the V2 input
+        // projection): eight independent loads issued together, ahead of the TMEM load.  (Fetching them a whole
+        // chunk ahead measured slower: 62 vs 54 us on the V2 shape -- the epilogue is issue-bound, not latency-bound.)
+        auto prefetch = [&](int c, float4 (&pre)[8]) {
+          const int n = n_base + c + c4 * 4;
+          const bool col_ok = n < N;                         // N % 4 == 0: a quad is inside or outside
+          float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ep.bias && col_ok) bias4 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            pre[it] = bias4;
+            if (ep.rowtab && col_ok && outrow[it] >= 0)
+              f4_add(pre[it], __ldg(reinterpret_cast<const float4*>(ep.rowtab + (size_t)tabrow[it] * ep.ld_tab + n)));
+          }
+        };
+        float4 pre[8];
         ptx::mbar_wait(&tfull_bar[buf], use & 1);
         ptx::tc_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
@@ -290,35 +312,41 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           if (n0 >= N) break;                                // warp-uniform
           uint32_t v[32];
           ptx::tmem_ld_32x32_nowait(taddr0 + c, v);
+          prefetch(c, pre);                                  // in flight during the TMEM load and the staging
           const int n = n0 + c4 * 4;
-          const bool col_ok = n < N;                         // N % 4 == 0: a quad is inside or outside
-          float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (ep.bias && col_ok) bias4 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
+          const bool col_ok = n < N;
           ptx::tmem_ld_wait_on(v);
           epi_stage(stg, lane, v);
           __syncwarp();
-#pragma unroll 4
+          float4 w[8];
+#pragma unroll
           for (int it = 0; it < 8; ++it) {
             const int rl = it * 4 + rsub;
-            float4 w = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
-            const int outrow = __shfl_sync(0xffffffffu, outrow_l, rl);
-            const int tabrow = __shfl_sync(0xffffffffu, tabrow_l, rl);
-            const int seqrow = __shfl_sync(0xffffffffu, seqrow_l, rl);
-            if (outrow < 0 || !col_ok) continue;
-            f4_add(w, bias4);
-            if (ep.rowtab) f4_add(w, __ldg(reinterpret_cast<const float4*>(ep.rowtab + (size_t)tabrow * ep.ld_tab + n)));
-            for (int cp = 0; cp < ncopy; ++cp) {
-              float4 o = w;
+            w[it] = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
+            f4_add(w[it], pre[it]);
+          }
+          for (int cp = 0; cp < ncopy; ++cp) {
+            float4 o[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {                 // all loads of the copy before any store
+              o[it] = w[it];
+              if (outrow[it] < 0 || !col_ok) continue;
               if (ep.seqbias)
-                f4_add(o, __ldg(reinterpret_cast<const float4*>(
-                              ep.seqbias + (size_t)(cp * ep.seq_count + seqrow) * ep.ld_seq + n)));
-              const size_t r = (size_t)outrow + (size_t)cp * ep.dup_row_stride;
-              if (ep.residual) f4_add(o, *reinterpret_cast<const float4*>(ep.residual + r * ep.ld_res + n));
-              if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + r * ep.ld_out + n) = o;
+                f4_add(o[it], __ldg(reinterpret_cast<const float4*>(
+                                  ep.seqbias + (size_t)(cp * ep.seq_count + seqrow[it]) * ep.ld_seq + n)));
+              if (ep.residual)
+                f4_add(o[it], *reinterpret_cast<const float4*>(
+                                  ep.residual + ((size_t)outrow[it] + (size_t)cp * ep.dup_row_stride) * ep.ld_res + n));
+            }
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              if (outrow[it] < 0 || !col_ok) continue;
+              const size_t r = (size_t)outrow[it] + (size_t)cp * ep.dup_row_stride;
+              if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + r * ep.ld_out + n) = o[it];
               if (ep.out_h16) {
                 uint2 pk;
-                pk.x = pack_h16x2(o.x, o.y, ep.h16_fmt);
-                pk.y = pack_h16x2(o.z, o.w, ep.h16_fmt);
+                pk.x = pack_h16x2(o[it].x, o[it].y, ep.h16_fmt);
+                pk.y = pack_h16x2(o[it].z, o[it].w, ep.h16_fmt);
                 *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(ep.out_h16) + r * ep.ld_out_h16 + n) = pk;
               }
             }

@@ -125,6 +125,17 @@ def main():
             rec("gemm out  N=263 K=512 ->f32 [B,J,T]", timed(lambda i: K.gemm(
                 Xa[i % ns], w_out, K.epilogue(bias=b_out, out_t=OUT[i % ns], t_s=S, t_t=T, t_skip=1), K=d), a.iters),
                 flops=2.0 * M * J * d, nbytes=M * d * esz + nb * B * J * T * 4)
+    if on("inproj2"):
+        B2, T2, nb2, kin2 = 128, 120, 2, 504
+        a2 = [rnd(B2 * T2, kin2, dtype=act) for _ in range(ns)]
+        w2 = rnd(d, kin2, dtype=act, scale=0.05)
+        AM = rnd(B2 * T2, d)
+        co = rnd(nb2 * B2, d)
+        XL = [torch.empty(nb2 * B2 * T2, d, device=dev) for _ in range(ns)]
+        rec("gemm in V2 N=512 K=498 AM+coarse dup2 ->f32", timed(lambda i: K.gemm(
+            a2[i % ns], w2, K.epilogue(rowtab=AM, tab_period=B2 * T2, tab_offset=0, seqbias=co, seq_rows=T2, seq_count=B2,
+                                       dup=nb2, dup_row_stride=B2 * T2, out_f32=XL[i % ns]), K=498), a.iters),
+            flops=2.0 * B2 * T2 * d * 498, nbytes=B2 * T2 * (kin2 * esz + d * 4) + nb2 * B2 * T2 * d * 4)
     if on("lattn"):
         nsq, T2, hd = 256, 120, 8
         e2 = d // hd
