@@ -39,11 +39,13 @@ __device__ __forceinline__ float4 philox_normal4(uint32_t g, uint32_t step, uint
   const float s = 2.3283064365386963e-10f;   // 2^-32
   const float u1 = ((float)r.x + 0.5f) * s, u2 = ((float)r.y + 0.5f) * s;
   const float u3 = ((float)r.z + 0.5f) * s, u4 = ((float)r.w + 0.5f) * s;
-  const float ra = sqrtf(-2.0f * logf(fminf(u1, 0.99999994f)));
-  const float rb = sqrtf(-2.0f * logf(fminf(u3, 0.99999994f)));
+  // Box-Muller with the hardware approximations (log2 / sin / cos on the special-function unit, ~2^-21 absolute
+  // error): this is a noise source, not a parity path -- parity runs inject their noise.
+  const float ta = -2.0f * __logf(fminf(u1, 0.99999994f)), tb = -2.0f * __logf(fminf(u3, 0.99999994f));
+  const float ra = ta * rsqrtf(ta), rb = tb * rsqrtf(tb);       // ta, tb >= 1.2e-7 > 0
   float sa, ca, sb, cb;
-  sincospif(2.0f * u2, &sa, &ca);
-  sincospif(2.0f * u4, &sb, &cb);
+  __sincosf(6.283185307179586f * u2, &sa, &ca);
+  __sincosf(6.283185307179586f * u4, &sb, &cb);
   return make_float4(ra * ca, ra * sa, rb * cb, rb * sb);
 }
 
@@ -72,7 +74,7 @@ __device__ __forceinline__ float post_one(float c, float u, float sc, bool has_u
   return mean + sigma * nz;
 }
 
-__global__ void __launch_bounds__(PS_THREADS)
+__global__ void __launch_bounds__(PS_THREADS, 5)
 posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
   extern __shared__ float tile[];                 // [PS_ROWS][T + pad] when a_next is requested
   const int b = blockIdx.y;
@@ -125,10 +127,11 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
     if (a.a_next) {
       const int f = 4 * i;
       const float ov[4] = {o.x, o.y, o.z, o.w};
+      int r = f / T, t = f - r * T;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const int r = (f + q) / T, t = (f + q) - r * T;
         tile[r * tstride + t] = ov[q];
+        if (++t == T) { t = 0; ++r; }
       }
     }
   }
@@ -172,8 +175,9 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
   // Device-side loop state: the last CTA to finish advances step and the model timesteps
   // (respace.py:124-129 map), so a captured step graph can be replayed without host involvement.
   if (a.next_t != nullptr && block_counter != nullptr) {
+    // No fence: the last CTA consumes nothing other CTAs wrote; it only has to overwrite *step_ptr after every CTA
+    // has read it, and each CTA's reads happen before its own barrier below (kernel-boundary ordering does the rest).
     __shared__ bool last;
-    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
       const uint32_t total = gridDim.x * gridDim.y;

@@ -136,6 +136,24 @@ def main():
             a2[i % ns], w2, K.epilogue(rowtab=AM, tab_period=B2 * T2, tab_offset=0, seqbias=co, seq_rows=T2, seq_count=B2,
                                        dup=nb2, dup_row_stride=B2 * T2, out_f32=XL[i % ns]), K=498), a.iters),
             flops=2.0 * B2 * T2 * d * 498, nbytes=B2 * T2 * (kin2 * esz + d * 4) + nb2 * B2 * T2 * d * 4)
+    if on("post"):
+        for (Bp, Jp, Tp) in ((64, 263, 196), (128, 498, 120)):
+            OUTp = [rnd(2 * Bp, Jp, Tp) for _ in range(ns)]
+            Xp = [rnd(Bp, Jp, Tp) for _ in range(ns)]
+            kin = (Jp + 26 + 7) // 8 * 8
+            Ap = [torch.zeros(Bp * Tp, kin, device=dev, dtype=act) for _ in range(ns)]
+            coef = torch.rand(6, 50, device=dev) * 0.5
+            stepp = torch.full((1,), 45, dtype=torch.int32, device=dev)
+            scale = torch.full((Bp,), 2.5, device=dev)
+            tmap = torch.arange(50, device=dev, dtype=torch.int64) * 20
+            nxt = torch.zeros(Bp, dtype=torch.int64, device=dev)
+
+            def run(i):
+                K.posterior_step(OUTp[i % ns][:Bp], Xp[i % ns], coef, stepp, Bp, Jp, Tp, uncond=OUTp[i % ns][Bp:],
+                                 scale=scale, x_prev=Xp[i % ns], a_next=Ap[i % ns], timestep_map=tmap, next_t=nxt,
+                                 seed=3, sample_base=0)
+            rec("posterior B=%d J=%d T=%d cfg philox" % (Bp, Jp, Tp), timed(run, a.iters),
+                nbytes=Bp * Jp * Tp * (4 * 4 + esz))
     if on("lattn"):
         nsq, T2, hd = 256, 120, 8
         e2 = d // hd
