@@ -131,6 +131,10 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return fmaxf(x, 0.f) - fabsf((0.5f * x) * e);
 }
 
+__device__ __forceinline__ void f4_add(float4& a, const float4 b) {
+  a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+}
+
 // ------------------------------------------------------------------ fused GEMM epilogue
 // Processes CH consecutive columns [n0, n0+CH) of logical row m.  See gdEpilogue in gd_b200.h.
 template <int CH>
@@ -223,62 +227,6 @@ __device__ __forceinline__ void epilogue_row_chunk(const gdEpilogue& ep, int m, 
         for (int i = 0; i < CH; ++i)
           if (i < nvalid) o[i] = cvt_h16(w[i], ep.h16_fmt);
       }
-    }
-  }
-}
-
-// Row-contiguous variant used by the shared-memory-staged tcgen05 epilogue: 4 consecutive columns
-// [n, n+4) of logical row m held by one lane, so that 8 lanes cover one 128-byte row segment and
-// every global access of the warp is a whole 32-byte sector.  `vec_ok` (kernel-uniform) says every
-// pointer / leading dimension of `ep` allows 16-byte (fp32) and 8-byte (16-bit) vector accesses;
-// column tails (N % 4 != 0) and unaligned operands take the scalar path above.
-__device__ __forceinline__ bool epilogue_vec_ok(const gdEpilogue& ep) {
-  auto al16 = [](const void* p) { return (reinterpret_cast<size_t>(p) & 15) == 0; };
-  bool ok = true;
-  if (ep.bias) ok = ok && al16(ep.bias);
-  if (ep.rowtab) ok = ok && al16(ep.rowtab) && (ep.ld_tab % 4 == 0);
-  if (ep.seqbias) ok = ok && al16(ep.seqbias) && (ep.ld_seq % 4 == 0);
-  if (ep.residual) ok = ok && al16(ep.residual) && (ep.ld_res % 4 == 0);
-  if (ep.out_f32) ok = ok && al16(ep.out_f32) && (ep.ld_out % 4 == 0);
-  if (ep.out_h16) ok = ok && al16(ep.out_h16) && (ep.ld_out_h16 % 4 == 0);
-  return ok && ep.out_t == nullptr;
-}
-
-__device__ __forceinline__ void f4_add(float4& a, const float4 b) {
-  a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-}
-
-__device__ __forceinline__ void epilogue_quad(const gdEpilogue& ep, bool vec_ok, int m, int n, int N, float4 v) {
-  if (!vec_ok || n + 4 > N) {
-    float s[4] = {v.x, v.y, v.z, v.w};
-    epilogue_row_chunk<4>(ep, m, n, N, s);
-    return;
-  }
-  if (ep.bias) f4_add(v, __ldg(reinterpret_cast<const float4*>(ep.bias + n)));
-  if (ep.rowtab)
-    f4_add(v, __ldg(reinterpret_cast<const float4*>(
-                  ep.rowtab + (size_t)((m % ep.tab_period) + ep.tab_offset) * ep.ld_tab + n)));
-  const int ncopy = ep.dup > 1 ? ep.dup : 1;
-  int base_row = m;
-  if (ep.map_t > 0) base_row = (m / ep.map_t) * ep.map_s + ep.map_off + (m % ep.map_t);
-  for (int c = 0; c < ncopy; ++c) {
-    float4 w = v;
-    if (ep.seqbias)
-      f4_add(w, __ldg(reinterpret_cast<const float4*>(
-                    ep.seqbias + (size_t)(c * ep.seq_count + m / ep.seq_rows) * ep.ld_seq + n)));
-    const size_t r = (size_t)base_row + (size_t)c * ep.dup_row_stride;
-    if (ep.residual) f4_add(w, *reinterpret_cast<const float4*>(ep.residual + r * ep.ld_res + n));
-    if (ep.act == GD_ACT_GELU_ERF) {
-      w.x = gelu_erf(w.x); w.y = gelu_erf(w.y); w.z = gelu_erf(w.z); w.w = gelu_erf(w.w);
-    } else if (ep.act == GD_ACT_SILU) {
-      w.x = silu(w.x); w.y = silu(w.y); w.z = silu(w.z); w.w = silu(w.w);
-    }
-    if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + r * ep.ld_out + n) = w;
-    if (ep.out_h16) {
-      uint2 p;
-      p.x = pack_h16x2(w.x, w.y, ep.h16_fmt);
-      p.y = pack_h16x2(w.z, w.w, ep.h16_fmt);
-      *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(ep.out_h16) + r * ep.ld_out_h16 + n) = p;
     }
   }
 }

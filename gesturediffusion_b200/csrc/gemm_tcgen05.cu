@@ -9,14 +9,17 @@
 // Epilogues are compile-time specialised (template EPI) so that each instantiation stays small
 // enough for the instruction cache (ncu on the first, fully runtime-dispatched version showed
 // stall_no_inst as the top stall):
-//   EPI_GENERIC            every gdEpilogue feature, one thread per accumulator row (used by the two
-//                          GEMMs per denoise step that need row maps / duplication / transposed stores)
 //   EPI_BIAS_H16           out_h16 = acc + bias                      (in_proj QKV)
 //   EPI_BIAS_GELU_H16      out_h16 = gelu_erf(acc + bias)            (linear1)
-//   EPI_BIAS_RES_F32       out_f32 = acc + bias + residual           (out_proj, linear2)
-// The specialised ones stage each 32x32 accumulator block through shared memory (XOR-swizzled, conflict
-// free) so that global stores are row-contiguous 64/128-byte segments, and fetch the residual one block
-// ahead of the TMEM read.
+//                          both: bias as warp-uniform register loads ahead of the accumulator wait, 16-bit pairs
+//                          staged in 128B-swizzled smem, one TMA store per [32 rows x 64 columns] box
+//   EPI_BIAS_RES_F32       out_f32 = acc + bias + residual           (out_proj / linear2 when not LayerNorm-fused)
+//   EPI_QUAD               bias, row table, per-sequence bias, residual, row map, copies on coalesced quads
+//                          (InputProcess of both denoisers)
+//   EPI_OUT_T              bias + transposed fp32 output             (OutputProcess + output[1:] + permute)
+//   EPI_GENERIC            every gdEpilogue feature, one thread per accumulator row (whatever is left)
+// RES_F32 / QUAD stage each 32x32 accumulator block through shared memory (XOR-swizzled, conflict free) so that
+// global accesses are row-contiguous 128-byte segments.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -48,8 +51,7 @@ struct GemmCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarBytes = 256;
   static constexpr int kStagingBytes = kEpiWarps * 32 * 32 * 4;                 // one 4 KB block per epilogue warp
-  static constexpr int kBiasBytes = 2 * BN * 4;                                 // bias slice of the tile, double buffered
-  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBiasBytes + kBarBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBarBytes;
   static constexpr int kTmemCols = 2 * BN;                                      // 256 or 512 (power of 2)
 };
 
@@ -79,34 +81,6 @@ __device__ __forceinline__ void epi_finish_f32(const gdEpilogue& ep, uint32_t st
   __syncwarp();
 }
 
-// 16-bit output: lane -> (row it*8 + lane/4, columns 8*(lane%4) .. +7): one 16-byte store per lane, 4 lanes cover
-// one 64-byte row segment.  b0/b1 = bias of the lane's 8 columns.
-template <bool GELU>
-__device__ __forceinline__ void epi_finish_h16(const gdEpilogue& ep, uint32_t stg, int lane, int m_warp, int n0, int M,
-                                               const float4 b0, const float4 b1) {
-  const int c8 = lane & 3, rsub = lane >> 2, n = n0 + c8 * 8;
-  uint16_t* out = reinterpret_cast<uint16_t*>(ep.out_h16);
-#pragma unroll
-  for (int it = 0; it < 4; ++it) {
-    const int rl = it * 8 + rsub, mm = m_warp + rl;
-    float4 w0 = ptx::lds_v4(stg + rl * 128 + (((2 * c8) ^ (rl & 7)) << 4));
-    float4 w1 = ptx::lds_v4(stg + rl * 128 + (((2 * c8 + 1) ^ (rl & 7)) << 4));
-    f4_add(w0, b0);
-    f4_add(w1, b1);
-    if constexpr (GELU) {
-      w0.x = gelu_fast(w0.x); w0.y = gelu_fast(w0.y); w0.z = gelu_fast(w0.z); w0.w = gelu_fast(w0.w);
-      w1.x = gelu_fast(w1.x); w1.y = gelu_fast(w1.y); w1.z = gelu_fast(w1.z); w1.w = gelu_fast(w1.w);
-    }
-    uint4 q;
-    q.x = pack_h16x2(w0.x, w0.y, ep.h16_fmt);
-    q.y = pack_h16x2(w0.z, w0.w, ep.h16_fmt);
-    q.z = pack_h16x2(w1.x, w1.y, ep.h16_fmt);
-    q.w = pack_h16x2(w1.z, w1.w, ep.h16_fmt);
-    if (mm < M) *reinterpret_cast<uint4*>(out + (size_t)mm * ep.ld_out_h16 + n) = q;
-  }
-  __syncwarp();
-}
-
 // residual block one step ahead: 8 independent 16-byte loads per lane in flight
 __device__ __forceinline__ void prefetch_residual(const gdEpilogue& ep, int lane, int m_warp, int n0, int M,
                                                   float4 (&pre)[8]) {
@@ -129,8 +103,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   const int n_workers = (int)gridDim.x / CG, worker = (int)blockIdx.x / CG;
   extern __shared__ __align__(1024) uint8_t smem[];          // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment
   uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
-  float* bias_s = reinterpret_cast<float*>(staging + Cfg::kStagingBytes);
-  uint8_t* bars = reinterpret_cast<uint8_t*>(bias_s) + Cfg::kBiasBytes;
+  uint8_t* bars = staging + Cfg::kStagingBytes;
   if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bars);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
@@ -438,21 +411,13 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
         constexpr int NCH = kColsPerWarp / 32;
         const int nch = min(NCH, (N - n_base + 31) / 32);    // specialised paths have N % 32 == 0
         float4 pre[8];
-        float4 bias[EPI == EPI_BIAS_RES_F32 ? NCH : 2 * NCH];
+        static_assert(EPI == EPI_BIAS_RES_F32, "the last epilogue branch is the fp32 + residual one");
+        float4 bias[NCH];
         if (nch > 0) {
-          if constexpr (EPI == EPI_BIAS_RES_F32) {
 #pragma unroll
-            for (int c = 0; c < NCH; ++c)
-              if (c < nch) bias[c] = __ldg(reinterpret_cast<const float4*>(ep.bias + n_base + c * 32 + (lane & 7) * 4));
-            prefetch_residual(ep, lane, m_warp, n_base, M, pre);
-          } else {
-#pragma unroll
-            for (int c = 0; c < NCH; ++c)
-              if (c < nch) {
-                bias[2 * c] = __ldg(reinterpret_cast<const float4*>(ep.bias + n_base + c * 32 + (lane & 3) * 8));
-                bias[2 * c + 1] = __ldg(reinterpret_cast<const float4*>(ep.bias + n_base + c * 32 + (lane & 3) * 8 + 4));
-              }
-          }
+          for (int c = 0; c < NCH; ++c)
+            if (c < nch) bias[c] = __ldg(reinterpret_cast<const float4*>(ep.bias + n_base + c * 32 + (lane & 7) * 4));
+          prefetch_residual(ep, lane, m_warp, n_base, M, pre);
         }
         ptx::mbar_wait(&tfull_bar[buf], use & 1);
         ptx::tc_fence_after();
@@ -466,15 +431,11 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
             ptx::tmem_ld_wait_on(v);
             epi_stage(stg, lane, v);
             if (c + 1 < nch) ptx::tmem_ld_32x32_nowait(taddr0 + (c + 1) * 32, v);   // overlaps the stores below
-            if constexpr (EPI == EPI_BIAS_RES_F32) {
-              float4 cur[8];
+            float4 cur[8];
 #pragma unroll
-              for (int it = 0; it < 8; ++it) cur[it] = pre[it];
-              if (c + 1 < nch) prefetch_residual(ep, lane, m_warp, n0 + 32, M, pre);
-              epi_finish_f32(ep, stg, lane, m_warp, n0, M, bias[c], cur);
-            } else {
-              epi_finish_h16<EPI == EPI_BIAS_GELU_H16>(ep, stg, lane, m_warp, n0, M, bias[2 * c], bias[2 * c + 1]);
-            }
+            for (int it = 0; it < 8; ++it) cur[it] = pre[it];
+            if (c + 1 < nch) prefetch_residual(ep, lane, m_warp, n0 + 32, M, pre);
+            epi_finish_f32(ep, stg, lane, m_warp, n0, M, bias[c], cur);
           }
         }
       }
