@@ -661,7 +661,12 @@ extern "C" int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ld
   const long tiles256 = (long)ceil_div(M, kBM) * ceil_div(N, 256);
   // (unless the last 256-wide column tile would be mostly padding, e.g. N = 263)
   const int pad256 = ceil_div(N, 256) * 256 - N, pad128 = ceil_div(N, 128) * 128 - N;
-  const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms) && (pad256 <= pad128);
+  static int bn_env = -1;                                    // GD_GEMM_BN=128 forces the narrow tile (experiments)
+  if (bn_env < 0) {
+    const char* e = getenv("GD_GEMM_BN");
+    bn_env = e ? atoi(e) : 0;
+  }
+  const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms) && (pad256 <= pad128) && bn_env != 128;
   const int epi = pick_epilogue(ep, N);
   cudaStream_t st = (cudaStream_t)stream;
   // CTA pairs (cta_group::2, 256 x 256 tiles) are implemented and parity-tested but opt-in (GD_GEMM_CG=2): at the
