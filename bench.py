@@ -9,7 +9,8 @@ One bench "step" = one full `p_sample_loop` call (D denoise steps) over one batc
 conditioning.  Workload at every N: BASELINE.json configs[1] per GPU -- MDM trans_enc (`MDM_Old`) d512 /
 8 layers / 4 heads, text-to-motion shape 263 x 196, batch 64 per GPU, CFG 2.5, random-init weights,
 synthetic conditioning; D = 50 respaced steps (the metric's "50-step CFG DDPM"); one extra
-1000-step call is timed and reported under "ddpm1000" (configs[1] quotes 1000 steps).
+1000-step call is timed and reported under "ddpm1000" (configs[1] quotes 1000 steps), a 50-step DDIM call under
+"ddim50" and, for the GENEA feature layout (--workload cfg3), a 4-chunk take under "take4".
 Weak scaling: per-GPU batch fixed, global batch = 64 * N, weights/seed broadcast once, motions
 all-gathered at the end of every call, no per-step collective.
 
@@ -284,6 +285,33 @@ def run_b200(args):
         ms1000 = timed(1, False, dif1000)
         extra["ddpm1000"] = {"value": B * world * T / (ms1000 * 1e-3), "unit": "frames/s",
                              "ms_per_denoise_step": ms1000 / 1000.0, "calls": 1}
+
+    # SURVEY 8.6 rows on the same workload, rank-local (no gather): 50-step DDIM (eta 0) and, for the 6-interleaved
+    # GENEA layout (cfg3), a 4-chunk take through generate_take (seed hand-off + de-normalise/split on the device)
+    if not args.skip_1000:
+        def timed_local(fn):
+            fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1)
+        dif_ddim = create_gaussian_diffusion(timestep_respacing="ddim%d" % D)
+        dif_ddim.rng, dif_ddim.seed, dif_ddim.sample_base = "philox", dif.seed, dif.sample_base
+        ms_ddim = timed_local(lambda: dif_ddim.ddim_sample_loop(model, shape, clip_denoised=False,
+                                                                model_kwargs={"y": y_dev}, eta=0.0))
+        extra["ddim%d" % D] = {"value": B * T / (ms_ddim * 1e-3), "unit": "frames/s per GPU",
+                               "ms_per_denoise_step": ms_ddim / D}
+        if J % 6 == 0 and use_cfg:
+            from gesturediffusion_b200.generate import generate_take
+            chunks = [y_dev] * 4
+            mean, std = torch.zeros(J, device=dev), torch.ones(J, device=dev)
+            ms_take = timed_local(lambda: generate_take(model, dif, chunks, B, T, seed_poses=cfg["seed_poses"],
+                                                        guidance_param=GUIDANCE, mean=mean, std=std))
+            extra["take4"] = {"value": 4 * B * T / (ms_take * 1e-3), "unit": "frames/s per GPU", "chunks": 4,
+                              "ms_per_denoise_step": ms_take / (4 * D)}
 
     # ---- roofline of the dominant kernel: CUDA events around every launch of one eager denoise pass
     peaks = measured_peaks()
