@@ -102,6 +102,18 @@ __device__ __forceinline__ uint32_t pack_h16x2(float lo, float hi, int fmt) {
   }
   return pack_bf16x2(lo, hi);
 }
+// inverse of pack_h16x2: (low half, high half) as floats
+__device__ __forceinline__ float2 unpack_h16x2(uint32_t u, int fmt) {
+  float2 f;
+  if (fmt == GD_FP16) {
+    asm("{\n\t.reg .f16 l, h;\n\tmov.b32 {l, h}, %2;\n\tcvt.f32.f16 %0, l;\n\tcvt.f32.f16 %1, h;\n\t}"
+        : "=f"(f.x), "=f"(f.y) : "r"(u));
+    return f;
+  }
+  f.x = __uint_as_float(u << 16);
+  f.y = __uint_as_float(u & 0xFFFF0000u);
+  return f;
+}
 __device__ __forceinline__ uint16_t cvt_h16(float v, int fmt) {
   return (uint16_t)(pack_h16x2(v, 0.f, fmt) & 0xFFFFu);
 }

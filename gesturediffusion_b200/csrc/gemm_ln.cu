@@ -16,6 +16,14 @@
 //   pass B  z = (y - mean) * rstd * gamma + beta from TMEM into swizzled staging blocks (fp32 128B swizzle, 16-bit
 //           64B swizzle), one TMA store per output and chunk (the hardware clips the ragged last tile).
 // Statistics are two-pass quality (no E[x^2] - mean^2 cancellation).
+//
+// MODE selects how the fp32 residual stream travels through HBM (the kernel's memory phases run at HBM speed, so
+// bytes are time):
+//   0  fp32 residual in, fp32 and / or 16-bit out (gd_gemm_h16_ln)
+//   1  fp32 residual in, split out: hi = round16(x), lo = round16(x - hi)  (gd_gemm_h16_ln_split, first sub-layer)
+//   2  split residual in (x = hi + lo, exact to ~2^-22 relative), split out
+// hi is the 16-bit operand the next GEMM needs anyway, so the split form costs 2 + 2 instead of 4 + 2 bytes per
+// element on the way out and the residual read is two 16-bit boxes instead of one fp32 box.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -45,8 +53,8 @@ struct LnCfg {
 
 struct LnParams {
   const float* bias; const float* gamma; const float* beta;
-  const float* residual; int ld_res;
-  float* out_f32; int ld_out;
+  const void* residual; int ld_res;   // fp32, or the 16-bit hi half of a split residual (MODE 2)
+  void* out_f32; int ld_out;          // fp32 output (MODE 0) or the 16-bit lo output (MODE 1 / 2)
   void* out_h16; int ld_out_h16; int h16_fmt;
   float eps;
   int M, K;
@@ -54,11 +62,15 @@ struct LnParams {
   int dbg;     // GD_LN_DBG diagnostics (results wrong): 1 no statistics exchange, 2 no global stores, 4 no residual, 8 no epilogue
 };
 
-template <int BN, int STAGES, bool ALIAS>
+template <int BN, int STAGES, bool ALIAS, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
 gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                       const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_o32,
-                       const __grid_constant__ CUtensorMap tmap_o16, const LnParams p) {
+                       const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_rlo,
+                       const __grid_constant__ CUtensorMap tmap_o32, const __grid_constant__ CUtensorMap tmap_o16,
+                       const LnParams p) {
+  // MODE 0: tmap_res fp32 residual, tmap_o32 fp32 output, tmap_o16 16-bit output (tmap_rlo unused)
+  // MODE 1: tmap_res fp32 residual, tmap_o32 = lo output, tmap_o16 = hi output
+  // MODE 2: tmap_res / tmap_rlo = hi / lo residual (16-bit, 64B swizzle), outputs as MODE 1
   using Cfg = LnCfg<BN, STAGES, ALIAS>;
   constexpr int kLnStages = STAGES;
   constexpr bool kAlias = Cfg::kAlias;
@@ -89,6 +101,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_w);
     ptx::prefetch_tensormap(&tmap_res);
+    if constexpr (MODE == 2) ptx::prefetch_tensormap(&tmap_rlo);
     ptx::prefetch_tensormap(&tmap_o32);
     ptx::prefetch_tensormap(&tmap_o16);
   }
@@ -194,8 +207,10 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       const int tl = g / NCH, c = g - tl * NCH;
       const uint32_t bar = rbar + (uint32_t)(g & 1) * 8;
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(4096) : "memory");
-      ptx::tma_load_2d_s(rbuf + (uint32_t)(g & 1) * 4096, &tmap_res, bar, n_warp + c * 32,
-                         (cluster_id + tl * n_clusters) * kLnBM + quarter * 32);
+      const int row0 = (cluster_id + tl * n_clusters) * kLnBM + quarter * 32;
+      const uint32_t dst = rbuf + (uint32_t)(g & 1) * 4096;
+      ptx::tma_load_2d_s(dst, &tmap_res, bar, n_warp + c * 32, row0);           // fp32 box, or the hi box (2 KB)
+      if constexpr (MODE == 2) ptx::tma_load_2d_s(dst + 2048, &tmap_rlo, bar, n_warp + c * 32, row0);
     };
     if (lane == 0 && !(p.dbg & 12)) {
       if (total_blocks > 0) issue_residual(0);
@@ -239,14 +254,37 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         }
         float v[32];
         const uint32_t rb = rbuf + (uint32_t)(g & 1) * 4096;
+        if constexpr (MODE == 2) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {                        // residual + bias while the TMEM load is in flight
-          const float4 r = ptx::lds_v4(rb + lane * 128 + ((j ^ (lane & 7)) << 4));
-          const float4 b = ptx::lds_v4(vec_s + (c * 32 + j * 4) * 4);
-          v[4 * j] = r.x + b.x;
-          v[4 * j + 1] = r.y + b.y;
-          v[4 * j + 2] = r.z + b.z;
-          v[4 * j + 3] = r.w + b.w;
+          for (int j = 0; j < 4; ++j) {                      // (hi + lo) + bias; 16-byte chunk j = columns 8j .. 8j+7
+            const uint32_t off = (uint32_t)lane * 64 + ((uint32_t)(j ^ ((lane >> 1) & 3)) << 4);
+            const uint4 h = ptx::lds_v4u(rb + off);
+            const uint4 l = ptx::lds_v4u(rb + 2048 + off);
+            const float4 b0 = ptx::lds_v4(vec_s + (c * 32 + j * 8) * 4);
+            const float4 b1 = ptx::lds_v4(vec_s + (c * 32 + j * 8 + 4) * 4);
+            const float2 h0 = unpack_h16x2(h.x, p.h16_fmt), h1 = unpack_h16x2(h.y, p.h16_fmt);
+            const float2 h2 = unpack_h16x2(h.z, p.h16_fmt), h3 = unpack_h16x2(h.w, p.h16_fmt);
+            const float2 l0 = unpack_h16x2(l.x, p.h16_fmt), l1 = unpack_h16x2(l.y, p.h16_fmt);
+            const float2 l2 = unpack_h16x2(l.z, p.h16_fmt), l3 = unpack_h16x2(l.w, p.h16_fmt);
+            v[8 * j] = (h0.x + l0.x) + b0.x;
+            v[8 * j + 1] = (h0.y + l0.y) + b0.y;
+            v[8 * j + 2] = (h1.x + l1.x) + b0.z;
+            v[8 * j + 3] = (h1.y + l1.y) + b0.w;
+            v[8 * j + 4] = (h2.x + l2.x) + b1.x;
+            v[8 * j + 5] = (h2.y + l2.y) + b1.y;
+            v[8 * j + 6] = (h3.x + l3.x) + b1.z;
+            v[8 * j + 7] = (h3.y + l3.y) + b1.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {                      // residual + bias while the TMEM load is in flight
+            const float4 r = ptx::lds_v4(rb + lane * 128 + ((j ^ (lane & 7)) << 4));
+            const float4 b = ptx::lds_v4(vec_s + (c * 32 + j * 4) * 4);
+            v[4 * j] = r.x + b.x;
+            v[4 * j + 1] = r.y + b.y;
+            v[4 * j + 2] = r.z + b.z;
+            v[4 * j + 3] = r.w + b.w;
+          }
         }
         ptx::fence_proxy_async();                            // our reads of the block precede the next TMA write
         __syncwarp();
@@ -309,6 +347,16 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       const float shift = -mean * rstd;
 
       // ---- pass B: normalise from TMEM into the swizzled staging blocks, one TMA store per output and chunk
+      // Split output with aliased staging (hi + lo of a chunk = one 4 KB ring block), two ways to use the 2 blocks:
+      //   default   block 1 stages every chunk, block 0 already receives the NEXT tile's first residual block
+      //             (requested here, a whole pass B ahead of its use)
+      //   dbg & 64  chunks alternate between the two blocks (a chunk never waits for the previous chunk's store)
+      constexpr bool kSplitAlias = (MODE != 0) && kAlias;
+      const bool dbl = kSplitAlias && (p.dbg & 64);
+      if (kSplitAlias && !dbl && lane == 0 && !(p.dbg & 4)) {
+        const int g = (local + 1) * NCH;                     // NCH is even: block g lives in ring slot 0
+        if (g < total_blocks) issue_residual(g);
+      }
 #pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
         float v[32];
@@ -327,34 +375,57 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           v[4 * j + 2] = fmaf(fmaf(v[4 * j + 2], rstd, shift), g.z, b.z);
           v[4 * j + 3] = fmaf(fmaf(v[4 * j + 3], rstd, shift), g.w, b.w);
         }
-        if (lane == 0) ptx::bulk_wait_read_all();            // the previous chunk's stores have read the staging
-        __syncwarp();
-        if (p.out_f32) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            ptx::sts_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2],
-                        v[4 * j + 3]);
+        if (lane == 0) {                                     // the staging block's previous stores have read it
+          if (dbl) ptx::bulk_wait_read_1();
+          else ptx::bulk_wait_read_all();
         }
-        if (p.out_h16) {
+        __syncwarp();
+        const uint32_t sth = kSplitAlias ? rbuf + (dbl ? (uint32_t)(c & 1) * 4096 : 4096u) : stg16;
+        const uint32_t stl = kSplitAlias ? sth + 2048 : stg;
+        if constexpr (MODE == 0) {
+          if (p.out_f32) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            ptx::sts_v4u(stg16 + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4),
-                         pack_h16x2(v[8 * j], v[8 * j + 1], p.h16_fmt), pack_h16x2(v[8 * j + 2], v[8 * j + 3], p.h16_fmt),
-                         pack_h16x2(v[8 * j + 4], v[8 * j + 5], p.h16_fmt),
-                         pack_h16x2(v[8 * j + 6], v[8 * j + 7], p.h16_fmt));
+            for (int j = 0; j < 8; ++j)
+              ptx::sts_v4(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2],
+                          v[4 * j + 3]);
+          }
+          if (p.out_h16) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              ptx::sts_v4u(stg16 + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4),
+                           pack_h16x2(v[8 * j], v[8 * j + 1], p.h16_fmt), pack_h16x2(v[8 * j + 2], v[8 * j + 3], p.h16_fmt),
+                           pack_h16x2(v[8 * j + 4], v[8 * j + 5], p.h16_fmt),
+                           pack_h16x2(v[8 * j + 6], v[8 * j + 7], p.h16_fmt));
+          }
+        } else {
+          // split output: hi = round16(z), lo = round16(z - hi); both as [32 x 32] 16-bit blocks (64B swizzle)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t hp[4], lp[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float a = v[8 * j + 2 * t], b = v[8 * j + 2 * t + 1];
+              hp[t] = pack_h16x2(a, b, p.h16_fmt);
+              const float2 f = unpack_h16x2(hp[t], p.h16_fmt);
+              lp[t] = pack_h16x2(a - f.x, b - f.y, p.h16_fmt);
+            }
+            const uint32_t off = (uint32_t)lane * 64 + ((uint32_t)(j ^ ((lane >> 1) & 3)) << 4);
+            ptx::sts_v4u(sth + off, hp[0], hp[1], hp[2], hp[3]);
+            if (p.out_f32) ptx::sts_v4u(stl + off, lp[0], lp[1], lp[2], lp[3]);   // out_f32 holds the lo pointer here
+          }
         }
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0 && !(p.dbg & 2)) {
-          if (p.out_f32) ptx::tma_store_2d(&tmap_o32, stg, n_warp + c * 32, m_warp);
-          if (p.out_h16) ptx::tma_store_2d(&tmap_o16, stg16, n_warp + c * 32, m_warp);
+          if (p.out_f32) ptx::tma_store_2d(&tmap_o32, MODE == 0 ? stg : stl, n_warp + c * 32, m_warp);
+          if (p.out_h16) ptx::tma_store_2d(&tmap_o16, MODE == 0 ? stg16 : sth, n_warp + c * 32, m_warp);
           ptx::bulk_commit();
         }
       }
       if (kAlias && lane == 0 && !(p.dbg & 4)) {             // staging has been read out: request the next tile's blocks
         const int g = (local + 1) * NCH;
         ptx::bulk_wait_read_all();
-        if (g < total_blocks) issue_residual(g);
+        if (g < total_blocks && !(kSplitAlias && !dbl)) issue_residual(g);
         if (g + 1 < total_blocks) issue_residual(g + 1);
       }
     }
@@ -370,14 +441,17 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   }
 }
 
-template <int BN, int STAGES, bool ALIAS>
+// MODE 0: p.residual / p.out_f32 are fp32.  MODE 1: p.residual fp32, p.out_f32 carries the lo output (16-bit,
+// leading dimension p.ld_out).  MODE 2: p.residual carries the hi residual and res_lo the lo residual (16-bit,
+// leading dimension p.ld_res), outputs as MODE 1.
+template <int BN, int STAGES, bool ALIAS, int MODE>
 static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p,
-                          cudaStream_t stream) {
+                          const void* res_lo, cudaStream_t stream) {
   using Cfg = LnCfg<BN, STAGES, ALIAS>;
   static bool attr_set = false;
   if (!attr_set) {
-    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    Cfg::kSmemBytes));
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
   CUtensorMap ta, tw;
@@ -386,11 +460,18 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   rc = make_tmap_2d(&tw, W, 2 * BN, p.K, ldw, BN, fmt);
   if (rc) return rc;
   CUtensorMap tr;
-  rc = make_tmap_2d_f32(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32);
+  if (MODE == 2) rc = make_tmap_2d_h16_sw64(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32, p.h16_fmt);
+  else rc = make_tmap_2d_f32(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32);
   if (rc) return rc;
+  CUtensorMap trlo = tr;
+  if (MODE == 2) {
+    rc = make_tmap_2d_h16_sw64(&trlo, res_lo, p.M, 2 * BN, p.ld_res, 32, p.h16_fmt);
+    if (rc) return rc;
+  }
   CUtensorMap to32 = tr, to16 = tr;                          // placeholders when an output is absent (never used)
   if (p.out_f32) {
-    rc = make_tmap_2d_f32(&to32, p.out_f32, p.M, 2 * BN, p.ld_out, 32);
+    if (MODE == 0) rc = make_tmap_2d_f32(&to32, p.out_f32, p.M, 2 * BN, p.ld_out, 32);
+    else rc = make_tmap_2d_h16_sw64(&to32, p.out_f32, p.M, 2 * BN, p.ld_out, 32, p.h16_fmt);
     if (rc) return rc;
   }
   if (p.out_h16) {
@@ -401,8 +482,8 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
   const int m_tiles = ceil_div(p.M, kLnBM);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS>, dim3(2 * clusters), dim3(kLnThreads), Cfg::kSmemBytes,
-                        stream, ta, tw, tr, to32, to16, p));
+  GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE>, dim3(2 * clusters),
+                        dim3(kLnThreads), Cfg::kSmemBytes, stream, ta, tw, tr, trlo, to32, to16, p));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }
@@ -452,7 +533,64 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
   }
   const bool deep = force_stages ? force_stages > 2 : true;
   if (N == 512)
-    return deep ? launch_gemm_ln<256, 3, true>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream)
-                : launch_gemm_ln<256, 2, false>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
-  return launch_gemm_ln<128, 3, false>(A, lda, W, ldw, fmt, p, (cudaStream_t)stream);
+    return deep ? launch_gemm_ln<256, 3, true, 0>(A, lda, W, ldw, fmt, p, nullptr, (cudaStream_t)stream)
+                : launch_gemm_ln<256, 2, false, 0>(A, lda, W, ldw, fmt, p, nullptr, (cudaStream_t)stream);
+  return launch_gemm_ln<128, 3, false, 0>(A, lda, W, ldw, fmt, p, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N,
+                                    int32_t K, int32_t fmt, const float* bias, const float* res_f32, int32_t ld_res,
+                                    const void* res_hi, const void* res_lo, int32_t ld_res16, const float* gamma,
+                                    const float* beta, float eps, void* out_hi, void* out_lo, int32_t ld_out16,
+                                    int32_t h16_fmt, void* stream) {
+  using namespace gd;
+  const bool split_in = res_f32 == nullptr;
+  GD_REQUIRE(A && W && bias && gamma && beta && out_hi, "gd_gemm_h16_ln_split: null pointer");
+  GD_REQUIRE(split_in ? (res_hi && res_lo) : (!res_hi && !res_lo),
+             "gd_gemm_h16_ln_split: give either res_f32 or both res_hi and res_lo");
+  GD_REQUIRE(M > 0 && K > 0, "gd_gemm_h16_ln_split: bad shape M=%d K=%d", M, K);
+  if (N != 256 && N != 512) {
+    set_error("gd_gemm_h16_ln_split: N=%d not in {256, 512}", N);
+    return GD_ERR_UNSUPPORTED;
+  }
+  GD_REQUIRE(fmt == GD_BF16 || fmt == GD_FP16, "gd_gemm_h16_ln_split: fmt must be GD_BF16 or GD_FP16");
+  GD_REQUIRE(h16_fmt == GD_BF16 || h16_fmt == GD_FP16, "gd_gemm_h16_ln_split: bad h16_fmt");
+  GD_REQUIRE(lda % 8 == 0 && ldw % 8 == 0 && lda >= K && ldw >= K,
+             "gd_gemm_h16_ln_split: lda/ldw must be multiples of 8 and >= K (lda=%d ldw=%d K=%d)", lda, ldw, K);
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  GD_REQUIRE(al16(A) && al16(W) && al16(res_f32) && al16(res_hi) && al16(res_lo) && al16(out_hi) && al16(out_lo),
+             "gd_gemm_h16_ln_split: operands must be 16-byte aligned");
+  GD_REQUIRE(ld_out16 >= N && ld_out16 % 8 == 0 &&
+                 (split_in ? (ld_res16 >= N && ld_res16 % 8 == 0) : (ld_res >= N && ld_res % 4 == 0)),
+             "gd_gemm_h16_ln_split: leading dimensions must be >= N and multiples of 8 (fp32 residual: 4)");
+  LnParams p;
+  p.bias = bias; p.gamma = gamma; p.beta = beta;
+  p.residual = split_in ? res_hi : (const void*)res_f32;
+  p.ld_res = split_in ? ld_res16 : ld_res;
+  p.out_f32 = out_lo; p.ld_out = ld_out16;
+  p.out_h16 = out_hi; p.ld_out_h16 = ld_out16; p.h16_fmt = h16_fmt;
+  p.eps = eps; p.M = M; p.K = K;
+  {
+    static int dbg = -1;
+    if (dbg < 0) {
+      const char* e = getenv("GD_LN_DBG");
+      dbg = e ? atoi(e) : 0;
+    }
+    p.dbg = dbg;
+  }
+  p.idesc = ptx::umma_idesc_h16_f32(kLnBM, N / 2, fmt == GD_FP16);
+  cudaStream_t st = (cudaStream_t)stream;
+  static int shallow_k = -1;                                 // GD_LN_SHALLOW_K=k: K <= k uses 2 stages + separate staging
+  if (shallow_k < 0) {
+    const char* e = getenv("GD_LN_SHALLOW_K");
+    shallow_k = e ? atoi(e) : 0;
+  }
+  if (N == 512 && K <= shallow_k)
+    return split_in ? launch_gemm_ln<256, 2, false, 2>(A, lda, W, ldw, fmt, p, res_lo, st)
+                    : launch_gemm_ln<256, 2, false, 1>(A, lda, W, ldw, fmt, p, nullptr, st);
+  if (N == 512)
+    return split_in ? launch_gemm_ln<256, 3, true, 2>(A, lda, W, ldw, fmt, p, res_lo, st)
+                    : launch_gemm_ln<256, 3, true, 1>(A, lda, W, ldw, fmt, p, nullptr, st);
+  return split_in ? launch_gemm_ln<128, 3, false, 2>(A, lda, W, ldw, fmt, p, res_lo, st)
+                  : launch_gemm_ln<128, 3, false, 1>(A, lda, W, ldw, fmt, p, nullptr, st);
 }

@@ -19,6 +19,8 @@ kernels, 1e-5 parity runs).
 """
 import math
 
+import os
+
 import torch
 
 from . import kernels as K
@@ -100,6 +102,8 @@ class DenoiserEngine:
             raise ValueError("latent_dim/num_heads must be 32, 64 or 128")
         self._ws = {}
         self.fuse_ln = True            # GEMM + residual + LayerNorm in one kernel where gd_gemm_h16_ln supports d
+        # residual stream between the fused kernels as a 16-bit (hi, lo) pair instead of fp32 (GD_SPLIT_RES=0: fp32)
+        self.split_residual = os.environ.get("GD_SPLIT_RES", "1") != "0"
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -205,6 +209,8 @@ class DenoiserEngine:
         ws["a_in"] = buf(B * T, _round_up(self.k_in, 8), dtype=act)
         ws["X32"] = buf(R, d)
         ws["Xa"] = buf(R, d, dtype=act) if self.h16 else ws["X32"]
+        if self.h16:
+            ws["Xlo"] = buf(R, d, dtype=act)
         ws["QKV"] = buf(R, 3 * d, dtype=act)
         ws["ATT"] = buf(R, d, dtype=act)
         ws["Y32"] = buf(R, d)
@@ -297,6 +303,18 @@ class DenoiserEngine:
             p = "l%d." % l
             K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(ws["QKV"])), K=d)
             K.attention(ws["QKV"], ws["ATT"], nb * B, S, self.H, dh)
+            if fused_ln and self.split_residual:
+                # same two fused kernels with the fp32 residual stream carried through HBM as a 16-bit pair
+                # (Xa = round16(x), Xlo = round16(x - Xa)): 4 instead of 6 bytes per element on the way out, and the
+                # hi half is the operand the next GEMM reads anyway.  Layer 0 takes the fp32 X32 of the input stage.
+                Xlo, last = ws["Xlo"], l == self.L - 1
+                res = dict(res_f32=X32) if l == 0 else dict(res_hi=Xa, res_lo=Xlo)
+                K.gemm_ln_split(ws["ATT"], w[p + "o.w"], w[p + "o.b"], w[p + "norm1.g"], w[p + "norm1.b"],
+                                out_hi=Xa, out_lo=Xlo, K=d, **res)
+                K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
+                K.gemm_ln_split(ws["Hh"], w[p + "f2.w"], w[p + "f2.b"], w[p + "norm2.g"], w[p + "norm2.b"],
+                                out_hi=Xa, out_lo=None if last else Xlo, res_hi=Xa, res_lo=Xlo, K=self.F)
+                continue
             if fused_ln:
                 # out_proj + residual + norm1 and linear2 + residual + norm2, each in ONE kernel (2-CTA cluster
                 # LayerNorm epilogue); the residual stream X32 is updated in place

@@ -131,6 +131,27 @@ def gemm_ln(a, w, bias, residual, gamma, beta, out_f32=None, out_h16=None, eps=1
     _cabi.check(rc, "gd_gemm_h16_ln")
 
 
+def gemm_ln_split(a, w, bias, gamma, beta, out_hi, out_lo=None, res_f32=None, res_hi=None, res_lo=None, eps=1e-5,
+                  K=None):
+    """gemm_ln with the residual stream carried as a 16-bit (hi, lo) pair: residual = res_f32 or res_hi + res_lo,
+    result written as out_hi = round16(x) and out_lo = round16(x - out_hi) (out_lo may be None)."""
+    lib = _cabi.load()
+    M, N = a.shape[0], w.shape[0]
+    K = a.shape[1] if K is None else K
+    r16 = res_hi if res_hi is not None else out_hi
+    with _Timed("gemm_ln_h16", M=M, N=N, K=K):
+        rc = lib.gd_gemm_h16_ln_split(_dev(a, a.dtype, "A"), a.stride(0), _dev(w, a.dtype, "W"), w.stride(0), M, N, K,
+                                      fmt_of(a), _dev(bias, torch.float32, "bias"),
+                                      _dev(res_f32, torch.float32, "res_f32"),
+                                      res_f32.stride(0) if res_f32 is not None else 0,
+                                      _dev(res_hi, out_hi.dtype, "res_hi"), _dev(res_lo, out_hi.dtype, "res_lo"),
+                                      r16.stride(0),
+                                      _dev(gamma, torch.float32, "gamma"), _dev(beta, torch.float32, "beta"), eps,
+                                      _dev(out_hi, "h16", "out_hi"), _dev(out_lo, out_hi.dtype, "out_lo"),
+                                      out_hi.stride(0), fmt_of(out_hi), _cabi.stream_handle())
+    _cabi.check(rc, "gd_gemm_h16_ln_split")
+
+
 def attention(qkv, out, n_seq, S, n_heads, head_dim):
     lib = _cabi.load()
     with _Timed("attention", n_seq=n_seq, S=S, H=n_heads, dh=head_dim):

@@ -95,6 +95,18 @@ int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32
                    const float* gamma, const float* beta, float eps, float* out_f32, int32_t ld_out,
                    void* out_h16, int32_t ld_out_h16, int32_t h16_fmt, void* stream);
 
+/* Same sub-layer tail with the fp32 residual stream carried through HBM as a 16-bit pair (the kernel's memory phases
+ * run at HBM speed): x = hi + lo with hi = round16(x) -- the operand the next GEMM reads anyway -- and
+ * lo = round16(x - hi), exact to ~2^-22 relative for fp16 / 2^-16 for bf16.  The residual comes either as fp32
+ * (res_f32, first sub-layer of the stack; res_hi = res_lo = NULL) or as a pair (res_f32 = NULL); the result leaves as
+ * out_hi and, unless NULL (last sub-layer), out_lo.  res_hi / res_lo may alias out_hi / out_lo.  All 16-bit arrays
+ * use h16_fmt and leading dimensions that are multiples of 8.  Same N restriction as gd_gemm_h16_ln. */
+int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
+                         int32_t fmt, const float* bias, const float* res_f32, int32_t ld_res,
+                         const void* res_hi, const void* res_lo, int32_t ld_res16,
+                         const float* gamma, const float* beta, float eps,
+                         void* out_hi, void* out_lo, int32_t ld_out16, int32_t h16_fmt, void* stream);
+
 /* Full softmax self-attention of nn.MultiheadAttention inside nn.TransformerEncoderLayer
  * (mdm.py:90-96,216; no mask, scale 1/sqrt(head_dim)).  qkv is the packed in_proj output
  * [n_seq*S, 3*d] (q | k | v, heads contiguous inside each); out is [n_seq*S, d]. */

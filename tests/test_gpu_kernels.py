@@ -243,6 +243,73 @@ def test_gemm_ln_repeatable_under_load(cuda_device):
                 assert torch.equal(o16, first16)
 
 
+@pytest.mark.parametrize("M,N,K", [(1, 512, 512), (127, 512, 512), (129, 256, 64), (1000, 512, 1024),
+                                   (128 * 150 + 77, 512, 512), (25216, 512, 1024)])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16"])
+def test_gemm_ln_split_residual(cuda_device, M, N, K, dtype):
+    """gd_gemm_h16_ln_split: the residual stream as a 16-bit (hi, lo) pair.  fp32 residual in -> pair out equals the
+    fp32 kernel's result split exactly (hi = round16(x), lo = round16(x - hi)); pair in (in place) -> pair out
+    equals the float64 LayerNorm of the reconstructed residual; hi-only output for the last sub-layer."""
+    Kn = _K()
+    tdt = TDT[dtype]
+    g = torch.Generator(device="cuda").manual_seed(M + N + 1)
+    a = torch.randn(M, K, device="cuda", generator=g).to(tdt)
+    w = (torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K)).to(tdt)
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g) * 2 + 0.5
+    gamma = 1 + 0.1 * torch.randn(N, device="cuda", generator=g)
+    beta = 0.1 * torch.randn(N, device="cuda", generator=g)
+    x32 = torch.empty_like(res)
+    Kn.gemm_ln(a, w, bias, res, gamma, beta, out_f32=x32)
+    hi = torch.zeros(M, N, device="cuda", dtype=tdt)
+    lo = torch.full((M, N), 7.0, device="cuda", dtype=tdt)
+    Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi, out_lo=lo, res_f32=res)
+    assert torch.equal(hi, x32.to(tdt))
+    assert torch.equal(lo, (x32 - hi.float()).to(tdt))
+    recon = hi.float() + lo.float()
+    assert rel_l2(recon, x32) < (3e-7 if dtype == "fp16" else 2e-5)
+    # pair in, in place, pair out: the next sub-layer
+    y = recon.double() + a.double() @ w.double().t() + bias.double()
+    ref = torch.nn.functional.layer_norm(y, (N,), gamma.double(), beta.double(), 1e-5)
+    hi2, lo2 = hi.clone(), lo.clone()
+    Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi2, out_lo=lo2, res_hi=hi2, res_lo=lo2)
+    assert rel_l2(hi2.float() + lo2.float(), ref) < (5e-6 if dtype == "fp16" else 3e-5)
+    x32b = torch.empty_like(res)
+    Kn.gemm_ln(a, w, bias, recon, gamma, beta, out_f32=x32b)      # fp32 kernel on the same reconstructed residual
+    assert torch.equal(hi2, x32b.to(tdt))
+    # hi only (last sub-layer), separate output, inputs untouched
+    hi3 = torch.zeros_like(hi)
+    Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi3, res_hi=hi, res_lo=lo)
+    assert torch.equal(hi3, hi2)
+    assert torch.equal(hi.float() + lo.float(), recon)
+
+
+def test_gemm_ln_split_repeatable_and_argument_checks(cuda_device):
+    from gesturediffusion_b200 import _cabi
+    Kn = _K()
+    M, Kd = 25216 - 37, 1024
+    g = torch.Generator(device="cuda").manual_seed(5)
+    a = torch.randn(M, Kd, device="cuda", generator=g).half()
+    w = (torch.randn(512, Kd, device="cuda", generator=g) / math.sqrt(Kd)).half()
+    bias, gamma, beta = (torch.randn(512, device="cuda", generator=g) for _ in range(3))
+    res = torch.randn(M, 512, device="cuda", generator=g)
+    rh = res.half()
+    rl = (res - rh.float()).half()
+    first = None
+    for it in range(16):
+        hi = torch.zeros(M, 512, device="cuda", dtype=torch.float16)
+        lo = torch.zeros_like(hi)
+        Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi, out_lo=lo, res_hi=rh, res_lo=rl)
+        if first is None:
+            first = (hi, lo)
+        else:
+            assert torch.equal(hi, first[0]) and torch.equal(lo, first[1])
+    with pytest.raises(_cabi.GdError):          # both residual forms at once
+        Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi, out_lo=lo, res_f32=res, res_hi=rh, res_lo=rl)
+    with pytest.raises(_cabi.GdError):          # half a pair
+        Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi, out_lo=lo, res_hi=rh)
+
+
 def test_gemm_ln_rejects_other_widths(cuda_device):
     from gesturediffusion_b200 import _cabi
     Kn = _K()
