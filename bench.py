@@ -333,7 +333,9 @@ def run_b200(args):
             # the GEMM+LayerNorm kernel); the weights stay L2-resident and are not counted
             def algo(n, m):
                 fl = 2.0 * m["M"] * m["N"] * m["K"]
-                by = m["M"] * m["K"] * 2.0 + (m["M"] * m["N"] * (4.0 + 4.0 + 2.0) if n == "gemm_ln_h16"
+                # GEMM+LN: fp32 residual in, fp32 + 16-bit out = 10 B per element; with the residual stream carried
+                # as a 16-bit (hi, lo) pair the wrapper records its own figure (m["rw"]: 4 in + 4 or 2 out)
+                by = m["M"] * m["K"] * 2.0 + (m["M"] * m["N"] * float(m.get("rw", 10)) if n == "gemm_ln_h16"
                                               else m["M"] * m["N"] * 2.0)
                 return fl, by
             fl_all = sum(algo(n, m)[0] * c for n, m, c, t in gemm)

@@ -139,7 +139,8 @@ def gemm_ln_split(a, w, bias, gamma, beta, out_hi, out_lo=None, res_f32=None, re
     M, N = a.shape[0], w.shape[0]
     K = a.shape[1] if K is None else K
     r16 = res_hi if res_hi is not None else out_hi
-    with _Timed("gemm_ln_h16", M=M, N=N, K=K):
+    # rw = residual + output bytes per element through HBM (bench.py's algorithmic-bytes figure)
+    with _Timed("gemm_ln_h16", M=M, N=N, K=K, rw=4 + (4 if out_lo is not None else 2)):
         rc = lib.gd_gemm_h16_ln_split(_dev(a, a.dtype, "A"), a.stride(0), _dev(w, a.dtype, "W"), w.stride(0), M, N, K,
                                       fmt_of(a), _dev(bias, torch.float32, "bias"),
                                       _dev(res_f32, torch.float32, "res_f32"),
