@@ -153,6 +153,26 @@ def gemm_ln_split(a, w, bias, gamma, beta, out_hi, out_lo=None, res_f32=None, re
     _cabi.check(rc, "gd_gemm_h16_ln_split")
 
 
+def ffn_ln_supported(x, N, F):
+    """gd_ffn_h16_ln_split covers 16-bit operands, N = 512 and F a multiple of 256 (>= 512)."""
+    return x.dtype in H16 and N == 512 and F >= 512 and F % 256 == 0
+
+
+def ffn_ln_split(x_hi, x_lo, w1, b1, w2, b2, gamma, beta, out_hi, out_lo=None, eps=1e-5):
+    """LayerNorm((x_hi + x_lo) + gelu(x_hi @ w1^T + b1) @ w2^T + b2) * gamma + beta in one kernel (the hidden
+    activation stays on chip); result as out_hi = round16(x'), out_lo = round16(x' - out_hi) (out_lo may be None)."""
+    lib = _cabi.load()
+    M, N, F = x_hi.shape[0], w2.shape[0], w1.shape[0]
+    with _Timed("ffn_ln_h16", M=M, N=N, F=F, rw=4 + (4 if out_lo is not None else 2)):
+        rc = lib.gd_ffn_h16_ln_split(_dev(x_hi, x_hi.dtype, "x_hi"), _dev(x_lo, x_hi.dtype, "x_lo"), x_hi.stride(0),
+                                     _dev(w1, x_hi.dtype, "W1"), w1.stride(0), _dev(b1, torch.float32, "b1"),
+                                     _dev(w2, x_hi.dtype, "W2"), w2.stride(0), _dev(b2, torch.float32, "b2"),
+                                     M, N, F, fmt_of(x_hi), _dev(gamma, torch.float32, "gamma"),
+                                     _dev(beta, torch.float32, "beta"), eps, _dev(out_hi, x_hi.dtype, "out_hi"),
+                                     _dev(out_lo, x_hi.dtype, "out_lo"), out_hi.stride(0), _cabi.stream_handle())
+    _cabi.check(rc, "gd_ffn_h16_ln_split")
+
+
 def attention(qkv, out, n_seq, S, n_heads, head_dim):
     lib = _cabi.load()
     with _Timed("attention", n_seq=n_seq, S=S, H=n_heads, dh=head_dim):

@@ -107,6 +107,18 @@ int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, int32_t ldw,
                          const float* gamma, const float* beta, float eps,
                          void* out_hi, void* out_lo, int32_t ld_out16, int32_t h16_fmt, void* stream);
 
+/* The whole feed-forward sub-layer of nn.TransformerEncoderLayer (mdm.py:90-96; torch's _ff_block + norm2, post-norm,
+ * erf-GELU) in one kernel, on the split residual stream of gd_gemm_h16_ln_split:
+ *   x' = LayerNorm((x_hi + x_lo) + gelu(x_hi @ W1^T + b1) @ W2^T + b2) * gamma + beta
+ * x_hi / x_lo / out_hi / out_lo are [M, N] 16-bit (fmt) with leading dimensions ld_x / ld_out, W1 is [F, N] (linear1),
+ * W2 is [N, F] (linear2); out_lo may be NULL (last sub-layer); the outputs may alias the inputs.  The hidden
+ * activation gelu(linear1) never goes to HBM.  N = 512 and F a multiple of 256 (>= 512); GD_ERR_UNSUPPORTED
+ * otherwise (callers use gd_gemm_h16 + gd_gemm_h16_ln_split). */
+int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t ld_x, const void* W1, int32_t ldw1,
+                        const float* b1, const void* W2, int32_t ldw2, const float* b2, int32_t M, int32_t N,
+                        int32_t F, int32_t fmt, const float* gamma, const float* beta, float eps,
+                        void* out_hi, void* out_lo, int32_t ld_out, void* stream);
+
 /* Full softmax self-attention of nn.MultiheadAttention inside nn.TransformerEncoderLayer
  * (mdm.py:90-96,216; no mask, scale 1/sqrt(head_dim)).  qkv is the packed in_proj output
  * [n_seq*S, 3*d] (q | k | v, heads contiguous inside each); out is [n_seq*S, d]. */

@@ -310,6 +310,80 @@ def test_gemm_ln_split_repeatable_and_argument_checks(cuda_device):
         Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi, out_lo=lo, res_hi=rh)
 
 
+@pytest.mark.parametrize("M,F", [(1, 512), (127, 1024), (300, 1024), (128 * 150 + 77, 1024), (25216, 1024),
+                                 (128 * 75, 2048)])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16"])
+def test_ffn_ln_split(cuda_device, M, F, dtype):
+    """gd_ffn_h16_ln_split (linear1 + GELU + linear2 + residual + LayerNorm in one kernel, H kept on chip) against
+    the float64 sub-layer on the same 16-bit inputs and against the two-kernel path it replaces."""
+    Kn = _K()
+    tdt = TDT[dtype]
+    N = 512
+    g = torch.Generator(device="cuda").manual_seed(M + F)
+    x = torch.randn(M, N, device="cuda", generator=g)
+    hi = x.to(tdt)
+    lo = (x - hi.float()).to(tdt)
+    w1 = (torch.randn(F, N, device="cuda", generator=g) / math.sqrt(N)).to(tdt)
+    w2 = (torch.randn(N, F, device="cuda", generator=g) / math.sqrt(F)).to(tdt)
+    b1 = 0.5 * torch.randn(F, device="cuda", generator=g)
+    b2 = torch.randn(N, device="cuda", generator=g)
+    gamma = 1 + 0.1 * torch.randn(N, device="cuda", generator=g)
+    beta = 0.1 * torch.randn(N, device="cuda", generator=g)
+    # the path it replaces
+    h = torch.empty(M, F, device="cuda", dtype=tdt)
+    Kn.gemm(hi, w1, Kn.epilogue(bias=b1, act=Kn.GD_ACT_GELU_ERF, out_h16=h))
+    hi_ref, lo_ref = torch.zeros_like(hi), torch.zeros_like(lo)
+    Kn.gemm_ln_split(h, w2, b2, gamma, beta, out_hi=hi_ref, out_lo=lo_ref, res_hi=hi, res_lo=lo)
+    # float64 sub-layer with the hidden activation rounded to 16 bit as both paths do
+    xr = hi.double() + lo.double()
+    hd = torch.nn.functional.gelu(hi.double() @ w1.double().t() + b1.double()).to(tdt).double()
+    ref = torch.nn.functional.layer_norm(xr + hd @ w2.double().t() + b2.double(), (N,), gamma.double(),
+                                         beta.double(), 1e-5)
+    out_hi = torch.full_like(hi, 3.0)
+    out_lo = torch.full_like(lo, 3.0)
+    Kn.ffn_ln_split(hi, lo, w1, b1, w2, b2, gamma, beta, out_hi=out_hi, out_lo=out_lo)
+    got = out_hi.float() + out_lo.float()
+    tol = 3e-5 if dtype == "fp16" else 3e-4
+    assert rel_l2(got, ref) < tol
+    assert rel_l2(hi_ref.float() + lo_ref.float(), ref) < tol
+    assert rel_l2(got, hi_ref.float() + lo_ref.float()) < tol
+    # in place, hi only (last sub-layer)
+    hi2, lo2 = hi.clone(), lo.clone()
+    Kn.ffn_ln_split(hi2, lo2, w1, b1, w2, b2, gamma, beta, out_hi=hi2)
+    assert torch.equal(hi2, out_hi)
+    assert torch.equal(lo2, lo)
+    # in place, pair out; repeatable
+    hi3, lo3 = hi.clone(), lo.clone()
+    Kn.ffn_ln_split(hi3, lo3, w1, b1, w2, b2, gamma, beta, out_hi=hi3, out_lo=lo3)
+    assert torch.equal(hi3, out_hi) and torch.equal(lo3, out_lo)
+
+
+def test_ffn_ln_split_repeatable_under_load_and_argument_checks(cuda_device):
+    from gesturediffusion_b200 import _cabi
+    Kn = _K()
+    M, N, F = 25216 - 37, 512, 1024
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(M, N, device="cuda", generator=g)
+    hi = x.half()
+    lo = (x - hi.float()).half()
+    w1 = (torch.randn(F, N, device="cuda", generator=g) / math.sqrt(N)).half()
+    w2 = (torch.randn(N, F, device="cuda", generator=g) / math.sqrt(F)).half()
+    b1, b2, gamma, beta = (torch.randn(n, device="cuda", generator=g) for n in (F, N, N, N))
+    first = None
+    for it in range(16):
+        oh, ol = torch.zeros_like(hi), torch.zeros_like(lo)
+        Kn.ffn_ln_split(hi, lo, w1, b1, w2, b2, gamma, beta, out_hi=oh, out_lo=ol)
+        if first is None:
+            first = (oh, ol)
+        else:
+            assert torch.equal(oh, first[0]) and torch.equal(ol, first[1])
+    with pytest.raises(_cabi.GdError, match="unsupported"):
+        Kn.ffn_ln_split(hi[:, :256], lo[:, :256], w1[:, :256], b1, w2[:256], b2[:256], gamma[:256], beta[:256],
+                        out_hi=torch.zeros(M, 256, device="cuda", dtype=torch.float16))
+    with pytest.raises(_cabi.GdError, match="unsupported"):
+        Kn.ffn_ln_split(hi, lo, w1[:384], b1[:384], w2[:, :384], b2, gamma, beta, out_hi=torch.zeros_like(hi))
+
+
 def test_gemm_ln_rejects_other_widths(cuda_device):
     from gesturediffusion_b200 import _cabi
     Kn = _K()

@@ -110,6 +110,16 @@ def main():
     if on("f2ln"):
         rec("gemm ffn2+LN N=512 K=1024 ->f32+h16", timed(lambda i: K.gemm_ln(Hh[i % ns], w_2, b_2, X32[i % ns], gam, bet, out_f32=X32[i % ns], out_h16=Xa[i % ns]), a.iters),
             flops=2.0 * M * d * F, nbytes=M * F * esz + M * d * (4 + 4 + esz))
+    Xlo = [rnd(M, d, dtype=act, scale=1e-3) for _ in range(ns)]
+    if on("olns"):
+        rec("gemm o+LN   split residual (hi,lo)", timed(lambda i: K.gemm_ln_split(ATT[i % ns], w_o, b_o, gam, bet, out_hi=Xa[i % ns], out_lo=Xlo[i % ns], res_hi=Xa[i % ns], res_lo=Xlo[i % ns]), a.iters),
+            flops=2.0 * M * d * d, nbytes=M * d * esz + M * d * 8)
+    if on("f2lns"):
+        rec("gemm ffn2+LN split residual (hi,lo)", timed(lambda i: K.gemm_ln_split(Hh[i % ns], w_2, b_2, gam, bet, out_hi=Xa[i % ns], out_lo=Xlo[i % ns], res_hi=Xa[i % ns], res_lo=Xlo[i % ns]), a.iters),
+            flops=2.0 * M * d * F, nbytes=M * F * esz + M * d * 8)
+    if on("ffnln"):
+        rec("ffn1+gelu+ffn2+LN fused (hi,lo)", timed(lambda i: K.ffn_ln_split(Xa[i % ns], Xlo[i % ns], w_1, b_1, w_2, b_2, gam, bet, out_hi=Xa[i % ns], out_lo=Xlo[i % ns]), a.iters),
+            flops=4.0 * M * d * F, nbytes=M * d * 8)
     if on("inproj") or on("outproj"):
         B, T, nb, J, kin = nseq // 2, S - 1, 2, 263, 296
         a_in = [rnd(B * T, kin, dtype=act) for _ in range(ns)]
