@@ -15,13 +15,23 @@
 // (M 128 x N 256 x K 128 per chunk) then runs in both CTAs from shared memory.  A chunk slot is recycled when the
 // GEMM2 MMAs of BOTH CTAs have retired: each CTA's tcgen05.commit multicasts its arrival to the pair.
 //
-// Roles (320 threads): warp 0 = TMA producer (one ring of 32 KB stages: [X 128x64 | W1 128x64] for GEMM1,
-// [W2 256x64] for GEMM2, in exactly the order the MMA thread consumes them), warp 1 = UMMA issuer, warps 2..9 =
-// epilogue: H chunks during the tile, then the LayerNorm tail of gemm_ln.cu (pass A: + b2 + residual -> TMEM with
-// running (mean, M2); statistics exchange by st.async; pass B: normalise -> swizzled staging -> TMA stores of
-// hi / lo).  Per epilogue warp two 4 KB blocks receive the residual and stage the outputs; one of them aliases the
-// warp's own slab of the locally produced H slot (free between the tile's last GEMM2 and the next tile's first
-// chunk), which is what lets a third operand stage fit.
+// The residual is added on the tensor pipe: after the tile's first GEMM2 pair, "Y[:, 64 s ..] += X_hi I^T + X_lo I^T"
+// with a 64 x 64 identity as the B operand (products with 1.0 and fp32 accumulation: the same sum the explicit add
+// makes), so the LayerNorm tail only READS the accumulator in pass A and needs no residual loads.
+//
+// Roles (320 threads): warps 0..7 = epilogue (H chunks during the tile, then the LayerNorm tail of gemm_ln.cu:
+// pass A statistics, exchange by st.async, pass B normalise -> swizzled staging -> TMA stores of hi / lo; the two
+// staging blocks per warp are a dedicated 4 KB block and the warp's own slab of the locally produced H slot), warp 8 =
+// TMA producer (one ring of 32 KB stages: [X 128x64 | W1 128x64] for GEMM1, [W2 256x64] for GEMM2,
+// [X_hi 128x64 | X_lo 128x64] for the residual, in exactly the order the MMA thread consumes them), warp 9 = UMMA
+// issuer.
+//
+// Status: parity-green and opt-in (GD_FUSE_FFN=1).  At d = 512, F = 1024, M = 25 216 it takes 86 us
+// against 82 us for gd_gemm_h16 (linear1 + GELU) + gd_gemm_h16_ln_split.  The in-kernel timeline (gd_ffn_trace,
+// tools/trace_ffn.py) shows why: a tcgen05.mma kind::f16 costs ~170-200 SM clocks whether N is 64, 128 or 256
+// (GD_GEMM_DBG=5 GD_GEMM_BN=128: 49 us against 28 us for N = 256 on the same flops), and TMEM (Y 256 columns + two
+// 128-column chunk accumulators = all 512 columns) forces N = 128 for GEMM1 and N = 64 for the residual MMAs: 224 MMA
+// instructions per tile and CTA instead of 128, ~40 k clocks per tile on the tensor pipe alone.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -30,6 +40,9 @@
 namespace gd {
 
 constexpr int kFfBM = 128, kFfBK = 64, kFfThreads = 320, kFfEpiWarps = 8;
+// warps 0..7 = epilogue; the two single-lane control warps get the HIGHEST warp ids of their scheduler partitions
+// (the arbiter favours them over the GELU-heavy epilogue warps, gemm_tcgen05.cu)
+constexpr int kFfProducerWarp = kFfEpiWarps, kFfMmaWarp = kFfEpiWarps + 1;
 constexpr int kFfD = 512;                      // model width: K of GEMM1, N of GEMM2 (two CTAs x 256 columns)
 constexpr int kFfBN = 256;                     // output columns per CTA
 constexpr int kFfCH = 128;                     // hidden columns per chunk
@@ -39,7 +52,8 @@ constexpr int kFfSlotBytes = 32768;            // one H chunk: two [128 rows x 6
 constexpr int kFfRingOff = 0;
 constexpr int kFfHbufOff = kFfStages * kFfStageBytes;
 constexpr int kFfLnOff = kFfHbufOff + 2 * kFfSlotBytes;            // dedicated 4 KB block per epilogue warp
-constexpr int kFfVecOff = kFfLnOff + kFfEpiWarps * 4096;           // b2 | gamma | beta slices of this CTA
+constexpr int kFfI64Off = kFfLnOff + kFfEpiWarps * 4096;           // 64 x 64 identity, K-major 128B swizzle (8 KB)
+constexpr int kFfVecOff = kFfI64Off + 8192;                        // b2 | gamma | beta slices of this CTA
 constexpr int kFfStatOff = kFfVecOff + 3 * kFfBN * 4;              // [parity][part][row] (mean, M2)
 constexpr int kFfBarOff = kFfStatOff + 2 * 4 * kFfBM * 8;
 constexpr int kFfSmemBytes = kFfBarOff + 512;
@@ -50,16 +64,17 @@ struct FfParams {
   int h16_fmt;
   float eps;
   int M, F;
-  uint32_t idesc1, idesc2;
+  uint32_t idesc1, idesc2, idesc3;
+  unsigned long long* trace;   // optional timeline buffer (gd_ffn_trace): 3 roles x 4096 entries of (tag << 48 | clock)
   int dbg;           // GD_FFN_DBG diagnostics (results wrong): 1 no GELU arithmetic, 2 no global stores, 4 no X loads,
                      // 8 no operand loads, 16 no H exchange between the CTAs, 32 no MMAs
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFfThreads, 1)
 ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w1,
-                      const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_rhi,
-                      const __grid_constant__ CUtensorMap tmap_rlo, const __grid_constant__ CUtensorMap tmap_ohi,
-                      const __grid_constant__ CUtensorMap tmap_olo, const FfParams p) {
+                      const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_xlo,
+                      const __grid_constant__ CUtensorMap tmap_ohi, const __grid_constant__ CUtensorMap tmap_olo,
+                      const FfParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* ring = smem + kFfRingOff;
@@ -75,11 +90,18 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   uint64_t* y_full = hempty + 2;
   uint64_t* y_empty = y_full + 1;
   uint64_t* stat_bar = y_empty + 1;                          // [2]
-  uint64_t* res_bar = stat_bar + 2;                          // [epilogue warp][2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 2 * kFfEpiWarps);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
+  // timeline of CTA 0: role 0 = epilogue warp 2 lane 0, role 1 = MMA thread, role 2 = TMA producer
+  int tr_n = 0;
+  unsigned long long* tr_buf = nullptr;
+  if (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp >= kFfEpiWarps))
+    tr_buf = p.trace + (warp == 0 ? 0 : (warp == kFfMmaWarp ? 4096 : 8192));
+  auto TR = [&](unsigned tag) {
+    if (tr_buf != nullptr && tr_n < 4096) tr_buf[tr_n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull);
+  };
   const int n_clusters = (int)gridDim.x >> 1, cluster_id = (int)blockIdx.x >> 1;
   const int M = p.M;
   const int m_tiles = (M + kFfBM - 1) / kFfBM;
@@ -88,16 +110,15 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   constexpr int kKB1 = kFfD / kFfBK;                         // 8 K blocks per GEMM1 chunk
   constexpr int kKB2 = kFfCH / kFfBK;                        // 2 K blocks per GEMM2 chunk
 
-  if (warp == 0 && lane == 0) {
+  if (warp == kFfProducerWarp && lane == 0) {
     ptx::prefetch_tensormap(&tmap_x);
     ptx::prefetch_tensormap(&tmap_w1);
     ptx::prefetch_tensormap(&tmap_w2);
-    ptx::prefetch_tensormap(&tmap_rhi);
-    ptx::prefetch_tensormap(&tmap_rlo);
+    ptx::prefetch_tensormap(&tmap_xlo);
     ptx::prefetch_tensormap(&tmap_ohi);
     ptx::prefetch_tensormap(&tmap_olo);
   }
-  if (warp == 1 && lane == 0) {
+  if (warp == kFfMmaWarp && lane == 0) {
     for (int s = 0; s < kFfStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
       ptx::mbar_init(&empty_bar[s], 1);
@@ -112,14 +133,26 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     ptx::mbar_init(hfull_rem, 1);
     ptx::mbar_init(y_full, 1);
     ptx::mbar_init(y_empty, kFfEpiWarps);
-    for (int i = 0; i < 2 * kFfEpiWarps; ++i) ptx::mbar_init(&res_bar[i], 1);
     ptx::fence_barrier_init();
   }
-  if (warp == 2) ptx::tmem_alloc(tmem_slot, 512);
+  if (warp == 0) ptx::tmem_alloc(tmem_slot, 512);
   for (int i = threadIdx.x; i < kFfBN; i += kFfThreads) {
     vecs[i] = p.b2[n_cta + i];
     vecs[kFfBN + i] = p.gamma[n_cta + i];
     vecs[2 * kFfBN + i] = p.beta[n_cta + i];
+  }
+  {
+    // I64[n][k] = (n == k) as a K-major 128B-swizzled UMMA B operand: row n = 128 bytes, 16-byte chunk c (k = 8c..8c+7)
+    // at position c ^ (n & 7).  "Y += X I^T" adds the residual on the tensor pipe (exact: products with 1.0).
+    const uint32_t one = (p.h16_fmt == GD_FP16) ? 0x3C00u : 0x3F80u;
+    const uint32_t i64_s = ptx::smem_u32(smem + kFfI64Off);
+    for (int idx = threadIdx.x; idx < 64 * 8; idx += kFfThreads) {
+      const int n = idx >> 3, c = idx & 7;
+      uint32_t w[4] = {0u, 0u, 0u, 0u};
+      if (c == (n >> 3)) w[(n & 7) >> 1] = one << (16 * (n & 1));
+      ptx::sts_v4u(i64_s + n * 128 + ((c ^ (n & 7)) << 4), w[0], w[1], w[2], w[3]);
+    }
+    ptx::fence_proxy_async();
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -129,13 +162,14 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   ptx::grid_dep_wait();                                      // prologue above overlaps the previous kernel's tail
   ptx::grid_dep_launch();
 
-  if (warp == 0) {
+  if (warp == kFfProducerWarp) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       auto load_g1 = [&](int m_blk, int i) {                 // own chunk i of the tile: global chunk 2 i + rank
         const int j = 2 * i + (int)rank;
+        TR(1);
         for (int kb = 0; kb < kKB1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = ring + stage * kFfStageBytes;
@@ -153,6 +187,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         }
       };
       auto load_g2 = [&](int j) {                            // W2[n_cta .. +256, chunk j's 128 hidden columns]
+        TR(2);
         for (int kb = 0; kb < kKB2; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = ring + stage * kFfStageBytes;
@@ -165,17 +200,28 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           if (++stage == kFfStages) { stage = 0; phase ^= 1; }
         }
       };
+      auto load_res = [&](int m_blk) {                       // [X_hi | X_lo] blocks of this CTA's 256 output columns
+        for (int sb = 0; sb < kFfBN / kFfBK; ++sb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = ring + stage * kFfStageBytes;
+          ptx::mbar_arrive_expect_tx(&full_bar[stage], kFfStageBytes);
+          ptx::tma_load_2d(sa, &tmap_x, &full_bar[stage], n_cta + sb * kFfBK, m_blk * kFfBM);
+          ptx::tma_load_2d(sa + 16384, &tmap_xlo, &full_bar[stage], n_cta + sb * kFfBK, m_blk * kFfBM);
+          if (++stage == kFfStages) { stage = 0; phase ^= 1; }
+        }
+      };
       for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters) {
         load_g1(m_blk, 0);
         load_g1(m_blk, 1);
         for (int i = 0; i < NC; ++i) {                       // same order as the MMA thread
           load_g2(2 * i + (int)rank);
           load_g2(2 * i + 1 - (int)rank);
+          if (i == 0) load_res(m_blk);
           if (i + 2 < NC) load_g1(m_blk, i + 2);
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kFfMmaWarp) {
     // ------------------------------------------------------------------ UMMA issuer
     if (lane == 0) {
       int stage = 0;
@@ -185,8 +231,10 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
       const uint32_t hbuf_s = ptx::smem_u32(smem + kFfHbufOff);
       auto g1 = [&]() {
         const uint32_t buf = g1n & 1u, use = g1n >> 1;
+        TR(10);
         ptx::mbar_wait(&hacc_empty[buf], (use & 1u) ^ 1u);   // the epilogue has drained this accumulator
         ptx::tc_fence_after();
+        TR(11);
         const uint32_t tmem_d = tmem_base + 256u + buf * 128u;
         for (int kb = 0; kb < kKB1; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
@@ -201,10 +249,12 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           if (++stage == kFfStages) { stage = 0; phase ^= 1; }
         }
         ptx::umma_commit(&hacc_full[buf]);
+        TR(12);
         ++g1n;
       };
       auto g2 = [&](int j, bool first) {
         const uint32_t slot = (uint32_t)j & 1u;
+        TR(20);
         if (slot == rank) {
           ptx::mbar_wait(hfull_loc, pairn & 1u);
         } else {
@@ -214,6 +264,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           }
         }
         ptx::tc_fence_after();
+        TR(21);
         for (int kb = 0; kb < kKB2; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
@@ -227,6 +278,24 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           if (++stage == kFfStages) { stage = 0; phase ^= 1; }
         }
         ptx::umma_commit_mc(&hempty[slot], 3);               // this CTA is done with the slot: tell both CTAs
+        TR(22);
+      };
+      const uint32_t i64_s = ptx::smem_u32(smem + kFfI64Off);
+      auto gres = [&]() {                                    // Y[:, 64 sb ..] += X_hi I^T + X_lo I^T: the residual
+        for (int sb = 0; sb < kFfBN / kFfBK; ++sb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(ring + stage * kFfStageBytes);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int k = 0; k < kFfBK / 16; ++k)
+              ptx::umma_h16(tmem_base + (uint32_t)(sb * kFfBK), ptx::umma_desc_k_sw128(sa + h * 16384 + k * 32),
+                            ptx::umma_desc_k_sw128(i64_s + k * 32), p.idesc3, 1u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);
+          if (++stage == kFfStages) { stage = 0; phase ^= 1; }
+        }
       };
       uint32_t t = 0;
       for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++t) {
@@ -243,14 +312,16 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           g2(2 * i + (int)rank, i == 0);
           g2(2 * i + 1 - (int)rank, false);
           ++pairn;
+          if (i == 0) gres();
           if (i + 2 < NC) g1();
         }
         ptx::umma_commit(y_full);
+        TR(30);
       }
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps
-    const int ew = warp - 2;
+    const int ew = warp;
     const int quarter = warp & 3;                            // TMEM lane quarter this warp may access
     const int half = ew >> 2;
     constexpr int CW = kFfBN / 2;                            // output columns per warp
@@ -262,10 +333,9 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
                           (uint32_t)quarter * 4096u;
     const uint32_t slab_peer = ptx::mapa(slab, rank ^ 1u);
     const uint32_t hfull_rem_peer = ptx::mapa(ptx::smem_u32(hfull_rem), rank ^ 1u);
-    // LayerNorm tail: block 0 (dedicated) and block 1 (= the slab) receive the residual and stage the outputs
+    // LayerNorm tail: block 0 (dedicated) and block 1 (= the slab) stage the outputs of alternate column chunks
     const uint32_t blk0 = ptx::smem_u32(smem + kFfLnOff) + (uint32_t)ew * 4096u;
     auto blk = [&](int c) { return (c & 1) ? slab : blk0; };
-    const uint32_t rbar = ptx::smem_u32(&res_bar[2 * ew]);
     const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;
     const uint32_t stats_s = ptx::smem_u32(smem + kFfStatOff);
     const uint32_t stats_cl[2] = {ptx::mapa(stats_s, rank), ptx::mapa(stats_s, rank ^ 1u)};
@@ -273,14 +343,6 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     const uint32_t sbar_cl[2] = {ptx::mapa(sbar_s, rank), ptx::mapa(sbar_s, rank ^ 1u)};
     const uint32_t part = rank * 2u + (uint32_t)half;
     const int n_warp = n_cta + half * CW;
-    auto issue_residual = [&](int m_blk, int c) {            // lane 0: (hi | lo) residual block of chunk c -> block c & 1
-      const uint32_t bar = rbar + (uint32_t)(c & 1) * 8;
-      ptx::mbar_arrive_expect_tx_s(bar, 4096);
-      const int row0 = m_blk * kFfBM + quarter * 32;
-      ptx::tma_load_2d_s(blk(c), &tmap_rhi, bar, n_warp + c * 32, row0);
-      ptx::tma_load_2d_s(blk(c) + 2048, &tmap_rlo, bar, n_warp + c * 32, row0);
-    };
-    if (lane == 0 && cluster_id < m_tiles) issue_residual(cluster_id, 0);
     uint32_t t = 0;
     for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++t) {
       // ================= H chunks of this tile: TMEM -> + b1 -> GELU -> 16 bit -> own slot + peer's slot
@@ -294,8 +356,10 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
 #pragma unroll
           for (int q = 0; q < 16; ++q) bq[q] = __ldg(reinterpret_cast<const float4*>(b1p + 4 * q));
         }
+        TR(40);
         ptx::mbar_wait(&hacc_full[buf], use & 1u);
         ptx::tc_fence_after();
+        TR(41);
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + 256u + buf * 128u + (uint32_t)half * 64u;
         uint32_t v0[32], v1[32];
         ptx::tmem_ld_32x32_nowait(taddr, v0);
@@ -305,6 +369,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&hacc_empty[buf]);   // GEMM1 of chunk i + 2 may overwrite the accumulator
+        TR(42);
         uint32_t pk[32];                                     // gelu(acc + b1) as 16-bit pairs: 64 hidden columns
 #pragma unroll
         for (int q = 0; q < 8; ++q) {                        // 16-byte chunk q = hidden columns 8q .. 8q+7 of the 64
@@ -324,7 +389,9 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         }
         // the slot is free when both CTAs' GEMM2 of the previous own chunk have retired (the arithmetic above
         // overlaps that turnaround)
+        TR(43);
         ptx::mbar_wait(&hempty[rank], (e1n & 1u) ^ 1u);
+        TR(44);
 #pragma unroll
         for (int q = 0; q < 8; ++q)
           ptx::sts_v4u(slab + lane * 128 + ((q ^ (lane & 7)) << 4), pk[4 * q], pk[4 * q + 1], pk[4 * q + 2],
@@ -335,83 +402,67 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           ptx::mbar_arrive(hfull_loc);
           if (!(p.dbg & 16)) ptx::bulk_copy_to_cluster(slab_peer, slab, 4096, hfull_rem_peer);
         }
+        TR(45);
       }
 
-      // ================= LayerNorm tail of the tile (gemm_ln.cu, split residual in / split out)
+      // ================= LayerNorm tail of the tile.  The accumulator already holds x + linear2(h) (the residual was
+      // added by the identity MMAs), so pass A only reads: y = acc + b2, running (mean, M2) by Chan's update.
       const uint32_t par = t & 1u, use2 = t >> 1;
       const int m_warp = m_blk * kFfBM + quarter * 32;
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * CW);
       if (ew == 0 && lane == 0) ptx::mbar_arrive_expect_tx(&stat_bar[par], 4 * kFfBM * 8);
-      // block 1 is this warp's slab of the local H slot: its last chunk has been consumed by both CTAs' GEMM2 (which
-      // also means the bulk copy out of it has completed)
-      ptx::mbar_wait(&hempty[rank], (t * (uint32_t)NC + (uint32_t)NC - 1u) & 1u);
-      if (lane == 0) issue_residual(m_blk, 1);
+      TR(50);
       ptx::mbar_wait(y_full, t & 1u);
       ptx::tc_fence_after();
-
-      // ---- pass A: y = acc + b2 + (hi + lo) -> TMEM, running row statistics
+      TR(51);
       float r_mean = 0.f, r_m2 = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < NCH; ++c) {
-        uint32_t vr[32];
-        ptx::tmem_ld_32x32_nowait(taddr0 + c * 32, vr);
-        ptx::mbar_wait_s(rbar + (uint32_t)(c & 1) * 8, (uint32_t)(c >> 1) & 1u);
-        float v[32];
-        const uint32_t rb = blk(c);
+      {
+        uint32_t va[32], vb[32];
+        ptx::tmem_ld_32x32_nowait(taddr0, va);
+        auto pass_a = [&](int c, uint32_t (&vr)[32]) {
+          float v[32];
+          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {                        // 16-byte chunk q = columns 8q .. 8q+7 (64B swizzle)
-          const uint32_t off = (uint32_t)lane * 64 + ((uint32_t)(q ^ ((lane >> 1) & 3)) << 4);
-          const uint4 h = ptx::lds_v4u(rb + off);
-          const uint4 l = ptx::lds_v4u(rb + 2048 + off);
-          const float4 b0 = ptx::lds_v4(vec_s + (c * 32 + q * 8) * 4);
-          const float4 b1 = ptx::lds_v4(vec_s + (c * 32 + q * 8 + 4) * 4);
-          const float2 h0 = unpack_h16x2(h.x, p.h16_fmt), h1 = unpack_h16x2(h.y, p.h16_fmt);
-          const float2 h2 = unpack_h16x2(h.z, p.h16_fmt), h3 = unpack_h16x2(h.w, p.h16_fmt);
-          const float2 l0 = unpack_h16x2(l.x, p.h16_fmt), l1 = unpack_h16x2(l.y, p.h16_fmt);
-          const float2 l2 = unpack_h16x2(l.z, p.h16_fmt), l3 = unpack_h16x2(l.w, p.h16_fmt);
-          v[8 * q] = (h0.x + l0.x) + b0.x;
-          v[8 * q + 1] = (h0.y + l0.y) + b0.y;
-          v[8 * q + 2] = (h1.x + l1.x) + b0.z;
-          v[8 * q + 3] = (h1.y + l1.y) + b0.w;
-          v[8 * q + 4] = (h2.x + l2.x) + b1.x;
-          v[8 * q + 5] = (h2.y + l2.y) + b1.y;
-          v[8 * q + 6] = (h3.x + l3.x) + b1.z;
-          v[8 * q + 7] = (h3.y + l3.y) + b1.w;
-        }
-        ptx::fence_proxy_async();                            // our reads of the block precede the next TMA write
-        __syncwarp();
-        if (lane == 0 && c + 2 < NCH) issue_residual(m_blk, c + 2);
-        ptx::tmem_ld_wait_on(vr);
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+          for (int q = 0; q < 8; ++q) {
+            const float4 b = ptx::lds_v4(vec_s + (c * 32 + q * 4) * 4);
+            v[4 * q] = __uint_as_float(vr[4 * q]) + b.x;
+            v[4 * q + 1] = __uint_as_float(vr[4 * q + 1]) + b.y;
+            v[4 * q + 2] = __uint_as_float(vr[4 * q + 2]) + b.z;
+            v[4 * q + 3] = __uint_as_float(vr[4 * q + 3]) + b.w;
+            s0 += v[4 * q];
+            s1 += v[4 * q + 1];
+            s2 += v[4 * q + 2];
+            s3 += v[4 * q + 3];
+          }
+          const float cm = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
+          float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          v[4 * q] += __uint_as_float(vr[4 * q]);
-          v[4 * q + 1] += __uint_as_float(vr[4 * q + 1]);
-          v[4 * q + 2] += __uint_as_float(vr[4 * q + 2]);
-          v[4 * q + 3] += __uint_as_float(vr[4 * q + 3]);
-          s0 += v[4 * q];
-          s1 += v[4 * q + 1];
-          s2 += v[4 * q + 2];
-          s3 += v[4 * q + 3];
-        }
-        ptx::tmem_st_32x32(taddr0 + c * 32, v);
-        const float cm = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
-        float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float d0 = v[4 * q] - cm, d1 = v[4 * q + 1] - cm, d2 = v[4 * q + 2] - cm, d3 = v[4 * q + 3] - cm;
-          q0 = fmaf(d0, d0, q0);
-          q1 = fmaf(d1, d1, q1);
-          q2 = fmaf(d2, d2, q2);
-          q3 = fmaf(d3, d3, q3);
-        }
-        const float cq = (q0 + q1) + (q2 + q3);
-        const float na = (float)(c * 32), nb = 32.f, nt = na + nb;       // Chan's update
-        const float delta = cm - r_mean;
-        r_mean += delta * (nb / nt);
-        r_m2 += cq + delta * delta * (na * nb / nt);
+          for (int q = 0; q < 8; ++q) {
+            const float d0 = v[4 * q] - cm, d1 = v[4 * q + 1] - cm, d2 = v[4 * q + 2] - cm, d3 = v[4 * q + 3] - cm;
+            q0 = fmaf(d0, d0, q0);
+            q1 = fmaf(d1, d1, q1);
+            q2 = fmaf(d2, d2, q2);
+            q3 = fmaf(d3, d3, q3);
+          }
+          const float cq = (q0 + q1) + (q2 + q3);
+          const float na = (float)(c * 32), nb = 32.f, nt = na + nb;
+          const float delta = cm - r_mean;
+          r_mean += delta * (nb / nt);
+          r_m2 += cq + delta * delta * (na * nb / nt);
+        };
+        // TMEM loads run one chunk ahead of the arithmetic (NCH = 4)
+        ptx::tmem_ld_wait_on(va);
+        ptx::tmem_ld_32x32_nowait(taddr0 + 32, vb);
+        pass_a(0, va);
+        ptx::tmem_ld_wait_on(vb);
+        ptx::tmem_ld_32x32_nowait(taddr0 + 64, va);
+        pass_a(1, vb);
+        ptx::tmem_ld_wait_on(va);
+        ptx::tmem_ld_32x32_nowait(taddr0 + 96, vb);
+        pass_a(2, va);
+        ptx::tmem_ld_wait_on(vb);
+        pass_a(3, vb);
       }
-      ptx::tmem_st_wait();
 
       // ---- exchange of the four partial (mean, M2) of every row (2 column halves x 2 CTAs)
       {
@@ -419,7 +470,12 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         ptx::st_async_v2(stats_cl[0] + off, r_mean, r_m2, sbar_cl[0] + par * 8u);
         ptx::st_async_v2(stats_cl[1] + off, r_mean, r_m2, sbar_cl[1] + par * 8u);
       }
+      // block 1 is this warp's slab of the local H slot: its last chunk has been consumed by both CTAs' GEMM2 (which
+      // also means the bulk copy out of it has completed)
+      TR(52);
+      ptx::mbar_wait(&hempty[rank], (t * (uint32_t)NC + (uint32_t)NC - 1u) & 1u);
       ptx::mbar_wait(&stat_bar[par], use2 & 1u);
+      TR(53);
       float mean = 0.f, m2 = 0.f;
       {
         float pm[4], pq[4];
@@ -448,12 +504,13 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         }
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
+          const float4 b2 = ptx::lds_v4(vec_s + (c * 32 + q * 4) * 4);
           const float4 g = ptx::lds_v4(vec_s + (kFfBN + c * 32 + q * 4) * 4);
           const float4 b = ptx::lds_v4(vec_s + (2 * kFfBN + c * 32 + q * 4) * 4);
-          v[4 * q] = fmaf(fmaf(v[4 * q], rstd, shift), g.x, b.x);
-          v[4 * q + 1] = fmaf(fmaf(v[4 * q + 1], rstd, shift), g.y, b.y);
-          v[4 * q + 2] = fmaf(fmaf(v[4 * q + 2], rstd, shift), g.z, b.z);
-          v[4 * q + 3] = fmaf(fmaf(v[4 * q + 3], rstd, shift), g.w, b.w);
+          v[4 * q] = fmaf(fmaf(v[4 * q] + b2.x, rstd, shift), g.x, b.x);
+          v[4 * q + 1] = fmaf(fmaf(v[4 * q + 1] + b2.y, rstd, shift), g.y, b.y);
+          v[4 * q + 2] = fmaf(fmaf(v[4 * q + 2] + b2.z, rstd, shift), g.z, b.z);
+          v[4 * q + 3] = fmaf(fmaf(v[4 * q + 3] + b2.w, rstd, shift), g.w, b.w);
         }
         if (lane == 0) ptx::bulk_wait_read_1();              // the store of chunk c - 2 has read this block
         __syncwarp();
@@ -480,11 +537,10 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           ptx::bulk_commit();
         }
       }
-      if (lane == 0) {                                       // staging read out: block 0 takes the next tile's first block
-        ptx::bulk_wait_read_all();
-        if (m_blk + n_clusters < m_tiles) issue_residual(m_blk + n_clusters, 0);
-      }
-      __syncwarp();                                          // ... and the slab may be written by the next tile's chunks
+      TR(54);
+      if (lane == 0) ptx::bulk_wait_read_all();              // staging read out before the slab takes the next tile's chunk
+      __syncwarp();
+      TR(55);
     }
     if (lane == 0) ptx::bulk_wait_all();                     // global writes complete before the CTA retires
   }
@@ -492,13 +548,21 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   ptx::tc_fence_before();
   __syncthreads();
   ptx::cluster_sync_all();                                   // no CTA exits while its peer may still write its smem
-  if (warp == 2) {
+  if (warp == 0) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 512);
   }
 }
 
 }  // namespace gd
+
+static unsigned long long* g_ffn_trace = nullptr;
+/* Debug only: timeline buffer (device, >= 3 * 4096 uint64) filled by CTA 0 of every later gd_ffn_h16_ln_split launch;
+ * NULL turns it off. */
+extern "C" int gd_ffn_trace(void* buf) {
+  g_ffn_trace = static_cast<unsigned long long*>(buf);
+  return GD_OK;
+}
 
 extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t ld_x, const void* W1, int32_t ldw1,
                                    const float* b1, const void* W2, int32_t ldw2, const float* b2, int32_t M,
@@ -524,8 +588,10 @@ extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t l
   p.has_lo = out_lo != nullptr;
   p.h16_fmt = fmt;
   p.eps = eps; p.M = M; p.F = F;
+  p.trace = g_ffn_trace;
   p.idesc1 = ptx::umma_idesc_h16_f32(kFfBM, kFfCH, fmt == GD_FP16);
   p.idesc2 = ptx::umma_idesc_h16_f32(kFfBM, kFfBN, fmt == GD_FP16);
+  p.idesc3 = ptx::umma_idesc_h16_f32(kFfBM, kFfBK, fmt == GD_FP16);
   {
     static int dbg = -1;
     if (dbg < 0) {
@@ -539,16 +605,14 @@ extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t l
     GD_CUDA_OK(cudaFuncSetAttribute(ffn_ln_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
     attr_set = true;
   }
-  CUtensorMap tx, tw1, tw2, trh, trl, toh, tol;
+  CUtensorMap tx, tw1, tw2, txl, toh, tol;
   int rc = make_tmap_2d(&tx, x_hi, M, N, ld_x, kFfBM, fmt);
   if (rc) return rc;
   rc = make_tmap_2d(&tw1, W1, F, N, ldw1, kFfCH, fmt);
   if (rc) return rc;
   rc = make_tmap_2d(&tw2, W2, N, F, ldw2, kFfBN, fmt);
   if (rc) return rc;
-  rc = make_tmap_2d_h16_sw64(&trh, x_hi, M, N, ld_x, 32, fmt);
-  if (rc) return rc;
-  rc = make_tmap_2d_h16_sw64(&trl, x_lo, M, N, ld_x, 32, fmt);
+  rc = make_tmap_2d(&txl, x_lo, M, N, ld_x, kFfBM, fmt);
   if (rc) return rc;
   rc = make_tmap_2d_h16_sw64(&toh, out_hi, M, N, ld_out, 32, fmt);
   if (rc) return rc;
@@ -562,7 +626,7 @@ extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t l
   const int m_tiles = ceil_div(M, kFfBM);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
   GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, ffn_ln_tcgen05_kernel, dim3(2 * clusters), dim3(kFfThreads), kFfSmemBytes,
-                        (cudaStream_t)stream, tx, tw1, tw2, trh, trl, toh, tol, p));
+                        (cudaStream_t)stream, tx, tw1, tw2, txl, toh, tol, p));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

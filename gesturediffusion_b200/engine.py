@@ -104,6 +104,9 @@ class DenoiserEngine:
         self.fuse_ln = True            # GEMM + residual + LayerNorm in one kernel where gd_gemm_h16_ln supports d
         # residual stream between the fused kernels as a 16-bit (hi, lo) pair instead of fp32 (GD_SPLIT_RES=0: fp32)
         self.split_residual = os.environ.get("GD_SPLIT_RES", "1") != "0"
+        # linear1 + GELU + linear2 + residual + LayerNorm as ONE kernel (gd_ffn_h16_ln_split).  Opt-in: parity-green, but
+        # at d = 512 / F = 1024 it measures 86 us against 82 us for the two kernels it replaces
+        self.fuse_ffn = os.environ.get("GD_FUSE_FFN", "0") == "1"
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -311,6 +314,10 @@ class DenoiserEngine:
                 res = dict(res_f32=X32) if l == 0 else dict(res_hi=Xa, res_lo=Xlo)
                 K.gemm_ln_split(ws["ATT"], w[p + "o.w"], w[p + "o.b"], w[p + "norm1.g"], w[p + "norm1.b"],
                                 out_hi=Xa, out_lo=Xlo, K=d, **res)
+                if self.fuse_ffn and K.ffn_ln_supported(Xa, d, self.F):
+                    K.ffn_ln_split(Xa, Xlo, w[p + "f1.w"], w[p + "f1.b"], w[p + "f2.w"], w[p + "f2.b"],
+                                   w[p + "norm2.g"], w[p + "norm2.b"], out_hi=Xa, out_lo=None if last else Xlo)
+                    continue
                 K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
                 K.gemm_ln_split(ws["Hh"], w[p + "f2.w"], w[p + "f2.b"], w[p + "norm2.g"], w[p + "norm2.b"],
                                 out_hi=Xa, out_lo=None if last else Xlo, res_hi=Xa, res_lo=Xlo, K=self.F)
@@ -334,6 +341,8 @@ class DenoiserEngine:
 
     def kernels_per_step(self):
         per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512)) else 7
+        if per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512 and self.F % 256 == 0:
+            per_layer = 4
         return 2 + (1 if self.arch == "v2" else 0) + per_layer * self.L + 1
 
     def flops_per_step(self, B, T, nb):

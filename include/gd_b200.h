@@ -119,6 +119,10 @@ int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t ld_x, const 
                         int32_t F, int32_t fmt, const float* gamma, const float* beta, float eps,
                         void* out_hi, void* out_lo, int32_t ld_out, void* stream);
 
+/* Debug aid (tools/trace_ffn.py): device buffer of >= 3 * 4096 uint64 that CTA 0 of every later
+ * gd_ffn_h16_ln_split launch fills with (tag << 48 | SM clock) records; NULL (default) turns it off. */
+int gd_ffn_trace(void* buf);
+
 /* Full softmax self-attention of nn.MultiheadAttention inside nn.TransformerEncoderLayer
  * (mdm.py:90-96,216; no mask, scale 1/sqrt(head_dim)).  qkv is the packed in_proj output
  * [n_seq*S, 3*d] (q | k | v, heads contiguous inside each); out is [n_seq*S, d]. */

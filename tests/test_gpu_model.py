@@ -64,6 +64,30 @@ def test_forward_matches_oracle_fresh_inputs(cuda_device, arch, precision):
         assert err < TOL[precision]
 
 
+@pytest.mark.parametrize("case", ["v1_humanml", "v2_gesture"])
+@pytest.mark.parametrize("precision", ["fp16", "bf16"])
+def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
+    """The opt-in one-kernel feed-forward sub-layer (gd_ffn_h16_ln_split, GD_FUSE_FFN=1) against the reference golden
+    and against the default two-kernel path."""
+    cfg, sd, x, y, gold = load_model_case(case)
+    m = build_product_model(cfg, sd, cuda_device, precision)
+    xd, yd, t = x.to(cuda_device), to_dev(y, cuda_device), gold["t"].to(cuda_device)
+    base = m(xd, t, yd).clone()
+    eng = m.engine()
+    assert not eng.fuse_ffn
+    n0 = eng.kernels_per_step()
+    eng.fuse_ffn = True
+    try:
+        assert eng.kernels_per_step() == n0 - cfg["num_layers"]
+        fused = m(xd, t, yd)
+    finally:
+        eng.fuse_ffn = False
+    err = rel_l2(fused, gold["cond"])
+    print("fused ffn %s %s: %.2e (vs two-kernel path %.2e)" % (case, precision, err, rel_l2(fused, base)))
+    assert err < TOL[precision]
+    assert rel_l2(fused, base) < TOL[precision]
+
+
 def test_v2_rejects_length_not_multiple_of_window(cuda_device):
     cfg, sd, x, y, gold = load_model_case("v2_small")
     m = build_product_model(cfg, sd, cuda_device, "fp32")
