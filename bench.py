@@ -327,7 +327,16 @@ def run_b200(args):
         dif.use_cuda_graph = True
         tot = sum(t for _, t in summ.values())
         breakdown = sorted(((n, dict(m), c, t) for (n, m), (c, t) in summ.items()), key=lambda r: -r[3])
-        gemm = [(n, m, c, t) for n, m, c, t in breakdown if n in ("gemm_h16", "gemm_ln_h16")]
+        # launches of one kernel at one (M, N, K) are one entry, whatever their residual / output byte variant (rw)
+        merged = {}
+        for n, m, c, t in breakdown:
+            if n not in ("gemm_h16", "gemm_ln_h16"):
+                continue
+            key = (n, m["M"], m["N"], m["K"])
+            c0_, t0_, b0_ = merged.get(key, (0, 0.0, 0.0))
+            merged[key] = (c0_ + c, t0_ + t, b0_ + c * float(m.get("rw", 10)))
+        gemm = sorted(((n, {"M": M_, "N": N_, "K": K_, "rw": b / c}, c, t) for (n, M_, N_, K_), (c, t, b) in merged.items()),
+                      key=lambda r: -r[3])
         if gemm:
             # algorithmic work per launch: 2MNK flops; bytes = A (16 bit) + outputs (+ fp32 residual for
             # the GEMM+LayerNorm kernel); the weights stay L2-resident and are not counted

@@ -53,7 +53,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   uint64_t* o_full = bars + 16;     uint64_t* slot_free = bars + 18;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: warp-uniform for the compiler (uniform role branches, MMA descriptors in the uniform
+  // datapath instead of an ELECT / R2UR waterfall around every UTCHMMA)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int S = p.S, Sp = p.Sp, n_qt = p.n_qt;
   const int kv_bytes = Sp * 256;                            // one K (or V): 2 slabs of [Sp rows x 128 B]
   const int slab = Sp * 128;
@@ -126,46 +128,56 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ UMMA issuer
-    if (lane == 0) {
+    // the whole warp runs the loop (uniform control flow, barrier waits by all lanes); one elected lane issues
+    {
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t q_u = __shfl_sync(0xffffffffu, ptx::smem_u32(q_smem), 0);
+      const uint32_t kv_u = __shfl_sync(0xffffffffu, ptx::smem_u32(kv_smem), 0);
       for (int u0 = 0; u0 < U; u0 += 2) {
         for (int e = 0; e < 2; ++e) {                       // S = Q K^T for the pair
           const int u = u0 + e;
           if (u >= U) break;
-          const int slot = u & 1, use = u >> 1, qt = qt_of(u), b = kvb_of(u);
+          const int slot = u & 1, use = u >> 1, b = kvb_of(u);
           ptx::mbar_wait(&slot_free[slot], (use & 1) ^ 1);
           ptx::mbar_wait(&q_full[slot], use & 1);
           if (first_of(u)) ptx::mbar_wait(&k_full[b], use & 1);
           ptx::tc_fence_after();
-          const uint32_t qa = ptx::smem_u32(q_smem + slot * kAtQBytes);
-          const uint32_t ka = ptx::smem_u32(kv_smem + b * 2 * kv_bytes);
-          const uint32_t td = tmem_base + (uint32_t)(slot * 256);
+          const uint32_t qa = q_u + (uint32_t)(slot * kAtQBytes);
+          const uint32_t ka = kv_u + (uint32_t)(b * 2 * kv_bytes);
+          const uint32_t td = tmem_u + (uint32_t)(slot * 256);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const uint64_t da = ptx::umma_desc_k_sw128(qa + (k >> 2) * 16384 + (k & 3) * 32);
-            const uint64_t db = ptx::umma_desc_k_sw128(ka + (k >> 2) * slab + (k & 3) * 32);
-            ptx::umma_h16(td, da, db, p.idesc_s, k != 0 ? 1u : 0u);
+            for (int k = 0; k < 8; ++k) {
+              const uint64_t da = ptx::umma_desc_k_sw128(qa + (k >> 2) * 16384 + (k & 3) * 32);
+              const uint64_t db = ptx::umma_desc_k_sw128(ka + (k >> 2) * slab + (k & 3) * 32);
+              ptx::umma_h16(td, da, db, p.idesc_s, k != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&s_full[slot]);
+            ptx::umma_commit(&q_empty[slot]);
+            if (last_of(u)) ptx::umma_commit(&k_empty[b]);
           }
-          ptx::umma_commit(&s_full[slot]);
-          ptx::umma_commit(&q_empty[slot]);
-          if (last_of(u)) ptx::umma_commit(&k_empty[b]);
+          __syncwarp();
         }
         for (int e = 0; e < 2; ++e) {                       // O = P V for the pair
           const int u = u0 + e;
           if (u >= U) break;
-          const int slot = u & 1, use = u >> 1, qt = qt_of(u), b = kvb_of(u);
+          const int slot = u & 1, use = u >> 1, b = kvb_of(u);
           ptx::mbar_wait(&p_ready[slot], use & 1);
           if (first_of(u)) ptx::mbar_wait(&v_full[b], use & 1);
           ptx::tc_fence_after();
-          const uint32_t va = ptx::smem_u32(kv_smem + b * 2 * kv_bytes + kv_bytes);
-          const uint32_t tp = tmem_base + (uint32_t)(slot * 256);
+          const uint32_t va = kv_u + (uint32_t)(b * 2 * kv_bytes + kv_bytes);
+          const uint32_t tp = tmem_u + (uint32_t)(slot * 256);
           const uint32_t to = tp + 128;
           const int ksteps = Sp >> 4;
-          for (int k = 0; k < ksteps; ++k) {
-            const uint64_t db = ptx::umma_desc_mn_sw128(va + k * 2048, (uint32_t)slab);
-            ptx::umma_h16_ts(to, tp + (uint32_t)(k * 8), db, p.idesc_o, k != 0 ? 1u : 0u);
+          if (ptx::elect_one()) {
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t db = ptx::umma_desc_mn_sw128(va + k * 2048, (uint32_t)slab);
+              ptx::umma_h16_ts(to, tp + (uint32_t)(k * 8), db, p.idesc_o, k != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&o_full[slot]);
+            if (last_of(u)) ptx::umma_commit(&v_empty[b]);
           }
-          ptx::umma_commit(&o_full[slot]);
-          if (last_of(u)) ptx::umma_commit(&v_empty[b]);
+          __syncwarp();
         }
       }
     }

@@ -92,7 +92,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   uint64_t* stat_bar = y_empty + 1;                          // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform
   const uint32_t rank = ptx::cluster_ctarank();
   // timeline of CTA 0: role 0 = epilogue warp 2 lane 0, role 1 = MMA thread, role 2 = TMA producer
   int tr_n = 0;
@@ -223,32 +223,39 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     }
   } else if (warp == kFfMmaWarp) {
     // ------------------------------------------------------------------ UMMA issuer
-    if (lane == 0) {
+    // the whole warp runs the schedule (uniform control flow, barrier waits by all lanes); one elected lane issues
+    {
       int stage = 0;
       uint32_t phase = 0;
       uint32_t g1n = 0;                                      // GEMM1 chunks issued so far (all tiles)
       uint32_t pairn = 0;                                    // chunk pairs consumed so far (all tiles)
-      const uint32_t hbuf_s = ptx::smem_u32(smem + kFfHbufOff);
+      const uint32_t smem_u = __shfl_sync(0xffffffffu, ptx::smem_u32(smem), 0);
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t hbuf_s = smem_u + kFfHbufOff;
       auto g1 = [&]() {
         const uint32_t buf = g1n & 1u, use = g1n >> 1;
         TR(10);
         ptx::mbar_wait(&hacc_empty[buf], (use & 1u) ^ 1u);   // the epilogue has drained this accumulator
         ptx::tc_fence_after();
         TR(11);
-        const uint32_t tmem_d = tmem_base + 256u + buf * 128u;
+        const uint32_t tmem_d = tmem_u + 256u + buf * 128u;
         for (int kb = 0; kb < kKB1; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          const uint32_t sa = ptx::smem_u32(ring + stage * kFfStageBytes);
+          const uint32_t sa = smem_u + (uint32_t)(kFfRingOff + stage * kFfStageBytes);
           const uint32_t sb = sa + 16384;
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kFfBK / 16; ++k)
-            if (!(p.dbg & 32)) ptx::umma_h16(tmem_d, ptx::umma_desc_k_sw128(sa + k * 32), ptx::umma_desc_k_sw128(sb + k * 32), p.idesc1,
-                          (kb | k) != 0 ? 1u : 0u);
-          ptx::umma_commit(&empty_bar[stage]);
+            for (int k = 0; k < kFfBK / 16; ++k)
+              if (!(p.dbg & 32)) ptx::umma_h16(tmem_d, ptx::umma_desc_k_sw128(sa + k * 32), ptx::umma_desc_k_sw128(sb + k * 32), p.idesc1,
+                            (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_commit(&empty_bar[stage]);
+          }
+          __syncwarp();
           if (++stage == kFfStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&hacc_full[buf]);
+        if (ptx::elect_one()) ptx::umma_commit(&hacc_full[buf]);
+        __syncwarp();
         TR(12);
         ++g1n;
       };
@@ -259,7 +266,8 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           ptx::mbar_wait(hfull_loc, pairn & 1u);
         } else {
           if (!(p.dbg & 16)) {
-            ptx::mbar_arrive_expect_tx(hfull_rem, kFfSlotBytes);   // the peer's 8 slabs are the transactions
+            if (ptx::elect_one()) ptx::mbar_arrive_expect_tx(hfull_rem, kFfSlotBytes);   // the peer's 8 slabs are the transactions
+            __syncwarp();
             ptx::mbar_wait(hfull_rem, pairn & 1u);
           }
         }
@@ -269,31 +277,38 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
           const uint32_t sa = hbuf_s + slot * kFfSlotBytes + (uint32_t)kb * 16384u;
-          const uint32_t sb = ptx::smem_u32(ring + stage * kFfStageBytes);
+          const uint32_t sb = smem_u + (uint32_t)(kFfRingOff + stage * kFfStageBytes);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kFfBK / 16; ++k)
-            if (!(p.dbg & 32)) ptx::umma_h16(tmem_base, ptx::umma_desc_k_sw128(sa + k * 32), ptx::umma_desc_k_sw128(sb + k * 32), p.idesc2,
-                          (first && kb == 0 && k == 0) ? 0u : 1u);
-          ptx::umma_commit(&empty_bar[stage]);
+            for (int k = 0; k < kFfBK / 16; ++k)
+              if (!(p.dbg & 32)) ptx::umma_h16(tmem_u, ptx::umma_desc_k_sw128(sa + k * 32), ptx::umma_desc_k_sw128(sb + k * 32), p.idesc2,
+                            (first && kb == 0 && k == 0) ? 0u : 1u);
+            ptx::umma_commit(&empty_bar[stage]);
+          }
+          __syncwarp();
           if (++stage == kFfStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit_mc(&hempty[slot], 3);               // this CTA is done with the slot: tell both CTAs
+        if (ptx::elect_one()) ptx::umma_commit_mc(&hempty[slot], 3);   // this CTA is done with the slot: tell both CTAs
+        __syncwarp();
         TR(22);
       };
-      const uint32_t i64_s = ptx::smem_u32(smem + kFfI64Off);
+      const uint32_t i64_s = smem_u + kFfI64Off;
       auto gres = [&]() {                                    // Y[:, 64 sb ..] += X_hi I^T + X_lo I^T: the residual
         for (int sb = 0; sb < kFfBN / kFfBK; ++sb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          const uint32_t sa = ptx::smem_u32(ring + stage * kFfStageBytes);
+          const uint32_t sa = smem_u + (uint32_t)(kFfRingOff + stage * kFfStageBytes);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < 2; ++h) {
 #pragma unroll
-            for (int k = 0; k < kFfBK / 16; ++k)
-              ptx::umma_h16(tmem_base + (uint32_t)(sb * kFfBK), ptx::umma_desc_k_sw128(sa + h * 16384 + k * 32),
-                            ptx::umma_desc_k_sw128(i64_s + k * 32), p.idesc3, 1u);
+              for (int k = 0; k < kFfBK / 16; ++k)
+                ptx::umma_h16(tmem_u + (uint32_t)(sb * kFfBK), ptx::umma_desc_k_sw128(sa + h * 16384 + k * 32),
+                              ptx::umma_desc_k_sw128(i64_s + k * 32), p.idesc3, 1u);
+            }
+            ptx::umma_commit(&empty_bar[stage]);
           }
-          ptx::umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == kFfStages) { stage = 0; phase ^= 1; }
         }
       };
@@ -315,7 +330,8 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           if (i == 0) gres();
           if (i + 2 < NC) g1();
         }
-        ptx::umma_commit(y_full);
+        if (ptx::elect_one()) ptx::umma_commit(y_full);
+        __syncwarp();
         TR(30);
       }
     }

@@ -89,7 +89,9 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   uint64_t* res_bar = stat_bar + 2;                          // [epilogue warp][2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 2 * kLnEpiWarps);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: warp-uniform for the compiler, so the role branches stay uniform and the MMA warp's
+  // descriptor arithmetic runs in the uniform datapath (no ELECT / R2UR waterfall around every UTCHMMA)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
   const int n_clusters = (int)gridDim.x >> 1, cluster_id = (int)blockIdx.x >> 1;
   const int M = p.M;
@@ -151,31 +153,38 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ UMMA issuer
-    if (lane == 0) {
+    // the whole warp runs the loop (uniform control flow, barrier waits by all lanes); one elected lane issues
+    {
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t smem_u = __shfl_sync(0xffffffffu, ptx::smem_u32(smem), 0);
       for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
         const int buf = local & 1;
         const uint32_t use = (uint32_t)(local >> 1);
         ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);
         ptx::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
+        const uint32_t tmem_d = tmem_u + (uint32_t)(buf * BN);
         for (int kb = 0; kb < k_blocks; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          const uint32_t sa = ptx::smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sa = smem_u + (uint32_t)(stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kABytes;
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kLnBK / 16; ++k) {
-            const uint64_t da = ptx::umma_desc_k_sw128(sa + k * 32);
-            const uint64_t db = ptx::umma_desc_k_sw128(sb + k * 32);
-            ptx::umma_h16(tmem_d, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kLnBK / 16; ++k) {
+              const uint64_t da = ptx::umma_desc_k_sw128(sa + k * 32);
+              const uint64_t db = ptx::umma_desc_k_sw128(sb + k * 32);
+              ptx::umma_h16(tmem_d, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&empty_bar[stage]);
           }
-          ptx::umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == kLnStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&tfull_bar[buf]);
+        if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[buf]);
+        __syncwarp();
       }
     }
   } else {

@@ -111,7 +111,9 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: the compiler then knows it is warp-uniform, keeps the role branches uniform and the
+  // MMA warp's descriptor arithmetic in the uniform datapath (no ELECT / R2UR waterfall around every UTCHMMA)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int m_tiles = (M + kBM * CG - 1) / (kBM * CG);
   const int n_tiles = (N + BN - 1) / BN;
@@ -176,37 +178,46 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
     }
   } else if (warp == kMmaWarp) {
     // ------------------------------------------------------------------ UMMA issuer
-    if (lane == 0 && rank == 0) {
+    // The whole warp runs the loop (uniform control flow, barrier waits by all lanes); one elected lane issues.
+    if (rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t smem_u = __shfl_sync(0xffffffffu, ptx::smem_u32(smem), 0);
       for (int tile = worker; tile < total_tiles; tile += n_workers, ++local) {
         const int buf = local & 1;
         const uint32_t use = (uint32_t)(local >> 1);
         if constexpr (CG == 2) ptx::mbar_wait_cluster(&tempty_bar[buf], (use & 1) ^ 1);
         else ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);     // epilogue drained this accumulator
         ptx::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
+        const uint32_t tmem_d = tmem_u + (uint32_t)(buf * BN);
         for (int kb = 0; kb < k_blocks; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          const uint32_t sa = ptx::smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sa = smem_u + (uint32_t)(stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kABytes;
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBK / kUmmaK; ++k) {
-            if (dbg & 2) break;                              // diagnostics: no MMAs
-            const uint64_t da = ptx::umma_desc_k_sw128(sa + k * kUmmaK * 2);
-            const uint64_t db = ptx::umma_desc_k_sw128(sb + k * kUmmaK * 2);
-            if constexpr (CG == 2) ptx::umma_h16_cg2(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-            else ptx::umma_h16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kBK / kUmmaK; ++k) {
+              if (dbg & 2) break;                            // diagnostics: no MMAs
+              const uint64_t da = ptx::umma_desc_k_sw128(sa + k * kUmmaK * 2);
+              const uint64_t db = ptx::umma_desc_k_sw128(sb + k * kUmmaK * 2);
+              if constexpr (CG == 2) ptx::umma_h16_cg2(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+              else ptx::umma_h16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            // smem slot reusable when the MMAs retire (in both CTAs of a pair)
+            if constexpr (CG == 2) ptx::umma_commit_cg2(&empty_bar[stage], 3);
+            else ptx::umma_commit(&empty_bar[stage]);
           }
-          // smem slot reusable when the MMAs retire (in both CTAs of a pair)
-          if constexpr (CG == 2) ptx::umma_commit_cg2(&empty_bar[stage], 3);
-          else ptx::umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        if constexpr (CG == 2) ptx::umma_commit_cg2(&tfull_bar[buf], 3);       // accumulators complete
-        else ptx::umma_commit(&tfull_bar[buf]);
+        if (ptx::elect_one()) {
+          if constexpr (CG == 2) ptx::umma_commit_cg2(&tfull_bar[buf], 3);     // accumulators complete
+          else ptx::umma_commit(&tfull_bar[buf]);
+        }
+        __syncwarp();
       }
     }
   } else {

@@ -107,6 +107,11 @@ class DenoiserEngine:
         # linear1 + GELU + linear2 + residual + LayerNorm as ONE kernel (gd_ffn_h16_ln_split).  Opt-in: parity-green, but
         # at d = 512 / F = 1024 it measures 86 us against 82 us for the two kernels it replaces
         self.fuse_ffn = os.environ.get("GD_FUSE_FFN", "0") == "1"
+        # The encoder stack of the two guidance branches (or of two halves of the batch) as two independent kernel
+        # chains on two streams: a persistent kernel's last, partly filled round of tiles (197 row tiles over 74
+        # clusters = 2.66 -> 3 rounds at the cfg2a shapes) then overlaps the other chain's next kernel.
+        self.split_streams = os.environ.get("GD_SPLIT_STREAMS", "0") == "1"
+        self._side_stream = None
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -300,49 +305,76 @@ class DenoiserEngine:
                               seq_rows=T, seq_count=B, dup=nb, dup_row_stride=B * T, out_f32=ws["XL"]), K=self.k_in)
             rc, rs = self.rope_tables(T)
             K.local_attention(ws["XL"], rc, rs, X32, xa_b, nb * B, T, d, self.cl_head, 10)
+        n_seq = nb * B
+        if self.split_streams and n_seq >= 2 and self.h16:
+            # two independent halves of the sequences (the two guidance branches when nb == 2), forked onto a side
+            # stream and joined before OutputProcess; rows of a half are contiguous in every workspace buffer
+            h0 = n_seq // 2
+            main = torch.cuda.current_stream()
+            if self._side_stream is None:
+                self._side_stream = torch.cuda.Stream(device=self.device)
+            side = self._side_stream
+            side.wait_stream(main)
+            self._encoder_stack(ws, 0, h0, S)
+            with torch.cuda.stream(side):
+                self._encoder_stack(ws, h0, n_seq, S)
+            main.wait_stream(side)
+        else:
+            self._encoder_stack(ws, 0, n_seq, S)
+        # OutputProcess + output[1:] + permute to [.,J,1,T] (mdm.py:219-222,372-380)
+        K.gemm(Xa, w["out.w"], K.epilogue(bias=w["out.b"], out_t=ws["OUT"], t_s=S, t_t=T, t_skip=1), K=d)
+
+    def _encoder_stack(self, ws, seq0, seq1, S):
+        """The L post-norm encoder layers (mdm.py:90-96,216) on sequences [seq0, seq1) of the workspace."""
+        d, w = self.d, self.w
+        r0, r1 = seq0 * S, seq1 * S
+        rows = lambda name: ws[name][r0:r1]
+        X32, Xa = rows("X32"), rows("Xa")
+        xa_b = Xa if self.h16 else None
+        QKV, ATT, Hh = rows("QKV"), rows("ATT"), rows("Hh")
         dh = d // self.H
         fused_ln = self.fuse_ln and self.h16 and d in (256, 512)
         for l in range(self.L):
             p = "l%d." % l
-            K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(ws["QKV"])), K=d)
-            K.attention(ws["QKV"], ws["ATT"], nb * B, S, self.H, dh)
+            K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(QKV)), K=d)
+            K.attention(QKV, ATT, seq1 - seq0, S, self.H, dh)
             if fused_ln and self.split_residual:
                 # same two fused kernels with the fp32 residual stream carried through HBM as a 16-bit pair
                 # (Xa = round16(x), Xlo = round16(x - Xa)): 4 instead of 6 bytes per element on the way out, and the
                 # hi half is the operand the next GEMM reads anyway.  Layer 0 takes the fp32 X32 of the input stage.
-                Xlo, last = ws["Xlo"], l == self.L - 1
+                Xlo, last = rows("Xlo"), l == self.L - 1
                 res = dict(res_f32=X32) if l == 0 else dict(res_hi=Xa, res_lo=Xlo)
-                K.gemm_ln_split(ws["ATT"], w[p + "o.w"], w[p + "o.b"], w[p + "norm1.g"], w[p + "norm1.b"],
+                K.gemm_ln_split(ATT, w[p + "o.w"], w[p + "o.b"], w[p + "norm1.g"], w[p + "norm1.b"],
                                 out_hi=Xa, out_lo=Xlo, K=d, **res)
                 if self.fuse_ffn and K.ffn_ln_supported(Xa, d, self.F):
                     K.ffn_ln_split(Xa, Xlo, w[p + "f1.w"], w[p + "f1.b"], w[p + "f2.w"], w[p + "f2.b"],
                                    w[p + "norm2.g"], w[p + "norm2.b"], out_hi=Xa, out_lo=None if last else Xlo)
                     continue
-                K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
-                K.gemm_ln_split(ws["Hh"], w[p + "f2.w"], w[p + "f2.b"], w[p + "norm2.g"], w[p + "norm2.b"],
+                K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(Hh)), K=d)
+                K.gemm_ln_split(Hh, w[p + "f2.w"], w[p + "f2.b"], w[p + "norm2.g"], w[p + "norm2.b"],
                                 out_hi=Xa, out_lo=None if last else Xlo, res_hi=Xa, res_lo=Xlo, K=self.F)
                 continue
             if fused_ln:
                 # out_proj + residual + norm1 and linear2 + residual + norm2, each in ONE kernel (2-CTA cluster
                 # LayerNorm epilogue); the residual stream X32 is updated in place
-                K.gemm_ln(ws["ATT"], w[p + "o.w"], w[p + "o.b"], X32, w[p + "norm1.g"], w[p + "norm1.b"],
+                K.gemm_ln(ATT, w[p + "o.w"], w[p + "o.b"], X32, w[p + "norm1.g"], w[p + "norm1.b"],
                           out_f32=X32, out_h16=xa_b, K=d)
-                K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
-                K.gemm_ln(ws["Hh"], w[p + "f2.w"], w[p + "f2.b"], X32, w[p + "norm2.g"], w[p + "norm2.b"],
+                K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(Hh)), K=d)
+                K.gemm_ln(Hh, w[p + "f2.w"], w[p + "f2.b"], X32, w[p + "norm2.g"], w[p + "norm2.b"],
                           out_f32=X32, out_h16=xa_b, K=self.F)
                 continue
-            K.gemm(ws["ATT"], w[p + "o.w"], K.epilogue(bias=w[p + "o.b"], residual=X32, out_f32=ws["Y32"]), K=d)
-            K.layernorm(ws["Y32"], w[p + "norm1.g"], w[p + "norm1.b"], out_f32=X32, out_h16=xa_b)
-            K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(ws["Hh"])), K=d)
-            K.gemm(ws["Hh"], w[p + "f2.w"], K.epilogue(bias=w[p + "f2.b"], residual=X32, out_f32=ws["Y32"]), K=self.F)
-            K.layernorm(ws["Y32"], w[p + "norm2.g"], w[p + "norm2.b"], out_f32=X32, out_h16=xa_b)
-        # OutputProcess + output[1:] + permute to [.,J,1,T] (mdm.py:219-222,372-380)
-        K.gemm(Xa, w["out.w"], K.epilogue(bias=w["out.b"], out_t=ws["OUT"], t_s=S, t_t=T, t_skip=1), K=d)
+            K.gemm(ATT, w[p + "o.w"], K.epilogue(bias=w[p + "o.b"], residual=X32, out_f32=rows("Y32")), K=d)
+            K.layernorm(rows("Y32"), w[p + "norm1.g"], w[p + "norm1.b"], out_f32=X32, out_h16=xa_b)
+            K.gemm(Xa, w[p + "f1.w"], K.epilogue(bias=w[p + "f1.b"], act=K.GD_ACT_GELU_ERF, **self._outs(Hh)), K=d)
+            K.gemm(Hh, w[p + "f2.w"], K.epilogue(bias=w[p + "f2.b"], residual=X32, out_f32=rows("Y32")), K=self.F)
+            K.layernorm(rows("Y32"), w[p + "norm2.g"], w[p + "norm2.b"], out_f32=X32, out_h16=xa_b)
 
     def kernels_per_step(self):
         per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512)) else 7
         if per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512 and self.F % 256 == 0:
             per_layer = 4
+        if self.split_streams and self.h16:
+            per_layer *= 2                                   # one chain per half of the sequences (n_seq >= 2)
         return 2 + (1 if self.arch == "v2" else 0) + per_layer * self.L + 1
 
     def flops_per_step(self, B, T, nb):
