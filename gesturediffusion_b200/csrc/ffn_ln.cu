@@ -15,7 +15,7 @@
 // (M 128 x N 256 x K 128 per chunk) then runs in both CTAs from shared memory.  A chunk slot is recycled when the
 // GEMM2 MMAs of BOTH CTAs have retired: each CTA's tcgen05.commit multicasts its arrival to the pair.
 //
-// The residual is added on the tensor pipe: after the tile's first GEMM2 pair, "Y[:, 64 s ..] += X_hi I^T + X_lo I^T"
+// The residual is added on the tensor pipe: at the start of a tile "Y[:, 64 s ..] = X_hi I^T + X_lo I^T"
 // with a 64 x 64 identity as the B operand (products with 1.0 and fp32 accumulation: the same sum the explicit add
 // makes), so the LayerNorm tail only READS the accumulator in pass A and needs no residual loads.
 //
@@ -213,10 +213,10 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
       for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters) {
         load_g1(m_blk, 0);
         load_g1(m_blk, 1);
+        load_res(m_blk);
         for (int i = 0; i < NC; ++i) {                       // same order as the MMA thread
           load_g2(2 * i + (int)rank);
           load_g2(2 * i + 1 - (int)rank);
-          if (i == 0) load_res(m_blk);
           if (i + 2 < NC) load_g1(m_blk, i + 2);
         }
       }
@@ -293,7 +293,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         TR(22);
       };
       const uint32_t i64_s = smem_u + kFfI64Off;
-      auto gres = [&]() {                                    // Y[:, 64 sb ..] += X_hi I^T + X_lo I^T: the residual
+      auto gres = [&]() {                                    // Y[:, 64 sb ..] = X_hi I^T + X_lo I^T: the residual opens the tile
         for (int sb = 0; sb < kFfBN / kFfBK; ++sb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
@@ -304,7 +304,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
 #pragma unroll
               for (int k = 0; k < kFfBK / 16; ++k)
                 ptx::umma_h16(tmem_u + (uint32_t)(sb * kFfBK), ptx::umma_desc_k_sw128(sa + h * 16384 + k * 32),
-                              ptx::umma_desc_k_sw128(i64_s + k * 32), p.idesc3, 1u);
+                              ptx::umma_desc_k_sw128(i64_s + k * 32), p.idesc3, (h | k) != 0 ? 1u : 0u);
             }
             ptx::umma_commit(&empty_bar[stage]);
           }
@@ -316,18 +316,18 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
       for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++t) {
         g1();
         g1();
+        // The residual MMAs initialise the output accumulator while the epilogue warps work on the tile's first H
+        // chunk (the tensor pipe would wait for it anyway); every GEMM2 MMA then accumulates.
+        ptx::mbar_wait(y_empty, (t & 1u) ^ 1u);              // the LayerNorm tail of the previous tile has left TMEM
+        ptx::tc_fence_after();
+        gres();
         for (int i = 0; i < NC; ++i) {
-          if (i == 0) {
-            ptx::mbar_wait(y_empty, (t & 1u) ^ 1u);          // the LayerNorm tail of the previous tile has left TMEM
-            ptx::tc_fence_after();
-          }
           // the slot turnaround (GEMM2 retired in both CTAs -> next chunk may be written) is the critical chain:
           // GEMM2 goes first, the locally produced chunk (no DSMEM hop) before the peer's; GEMM1 of chunk i + 2
           // has slack (double-buffered accumulator) and fills the tensor pipe behind it
-          g2(2 * i + (int)rank, i == 0);
+          g2(2 * i + (int)rank, false);
           g2(2 * i + 1 - (int)rank, false);
           ++pairn;
-          if (i == 0) gres();
           if (i + 2 < NC) g1();
         }
         if (ptx::elect_one()) ptx::umma_commit(y_full);
