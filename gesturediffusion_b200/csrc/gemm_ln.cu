@@ -136,7 +136,8 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // (whole warp in uniform control flow, one elected lane issues)
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters) {
@@ -144,9 +145,12 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kLnBK, m_blk * kLnBM);
-          ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kLnBK, n_cta);
+          if (ptx::elect_one()) {
+            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kLnBK, m_blk * kLnBM);
+            ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kLnBK, n_cta);
+          }
+          __syncwarp();
           if (++stage == kLnStages) { stage = 0; phase ^= 1; }
         }
       }

@@ -150,28 +150,33 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
 
   if (warp == kProducerWarp) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // (whole warp in uniform control flow, one elected lane issues: tensor-map / barrier operands stay uniform)
+    {
       int stage = 0;
       uint32_t phase = 0;
+      uint8_t* const smem_u = smem;
       for (int tile = worker; tile < total_tiles; tile += n_workers) {
         const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
         for (int kb = 0; kb < k_blocks; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sa = smem_u + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          if (dbg & 4) {                                     // diagnostics: no operand traffic
-            if (rank == 0) ptx::mbar_arrive(&full_bar[stage]);
-          } else if constexpr (CG == 2) {
-            // both CTAs' bytes are credited to the LEADER's full barrier (its MMA thread is the only consumer)
-            const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
-            if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
-            ptx::tma_load_2d_cg2(sa, &tmap_a, fb, kb * kBK, (m_blk * 2 + (int)rank) * kBM);
-            ptx::tma_load_2d_cg2(sb, &tmap_w, fb, kb * kBK, n_blk * BN + (int)rank * (BN / 2));
-          } else {
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-            ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
-            ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kBK, n_blk * BN);
+          if (ptx::elect_one()) {
+            if (dbg & 4) {                                   // diagnostics: no operand traffic
+              if (rank == 0) ptx::mbar_arrive(&full_bar[stage]);
+            } else if constexpr (CG == 2) {
+              // both CTAs' bytes are credited to the LEADER's full barrier (its MMA thread is the only consumer)
+              const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+              if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+              ptx::tma_load_2d_cg2(sa, &tmap_a, fb, kb * kBK, (m_blk * 2 + (int)rank) * kBM);
+              ptx::tma_load_2d_cg2(sb, &tmap_w, fb, kb * kBK, n_blk * BN + (int)rank * (BN / 2));
+            } else {
+              ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+              ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
+              ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kBK, n_blk * BN);
+            }
           }
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
