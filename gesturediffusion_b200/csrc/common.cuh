@@ -15,6 +15,7 @@ namespace gd {
 // ------------------------------------------------------------------ host-side error plumbing
 void set_error(const char* fmt, ...);
 extern std::atomic<long long> g_launches;
+extern unsigned long long* g_ffn_trace;     // debug timeline buffer (gd_ffn_trace), NULL = off
 
 #define GD_REQUIRE(cond, ...)                                 \
   do {                                                        \

@@ -572,7 +572,8 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
 
 }  // namespace gd
 
-static unsigned long long* g_ffn_trace = nullptr;
+namespace gd { unsigned long long* g_ffn_trace = nullptr; }
+using gd::g_ffn_trace;
 /* Debug only: timeline buffer (device, >= 3 * 4096 uint64) filled by CTA 0 of every later gd_ffn_h16_ln_split launch;
  * NULL turns it off. */
 extern "C" int gd_ffn_trace(void* buf) {
