@@ -26,12 +26,12 @@
 // [X_hi 128x64 | X_lo 128x64] for the residual, in exactly the order the MMA thread consumes them), warp 9 = UMMA
 // issuer.
 //
-// Status: parity-green and opt-in (GD_FUSE_FFN=1).  At d = 512, F = 1024, M = 25 216 it takes 86 us
-// against 82 us for gd_gemm_h16 (linear1 + GELU) + gd_gemm_h16_ln_split.  The in-kernel timeline (gd_ffn_trace,
-// tools/trace_ffn.py) shows why: a tcgen05.mma kind::f16 costs ~170-200 SM clocks whether N is 64, 128 or 256
-// (GD_GEMM_DBG=5 GD_GEMM_BN=128: 49 us against 28 us for N = 256 on the same flops), and TMEM (Y 256 columns + two
-// 128-column chunk accumulators = all 512 columns) forces N = 128 for GEMM1 and N = 64 for the residual MMAs: 224 MMA
-// instructions per tile and CTA instead of 128, ~40 k clocks per tile on the tensor pipe alone.
+// Status: parity-green and opt-in (GD_FUSE_FFN=1).  At d = 512, F = 1024, M = 25 216 it takes 75 us
+// against 77.5 us for gd_gemm_h16 (linear1 + GELU) + gd_gemm_h16_ln_split in the loop benchmark and gives the same
+// step time (inside the step graph the two-kernel path finds most of H still in L2).  The in-kernel timeline
+// (gd_ffn_trace, tools/trace_ffn.py) shows the limits: TMEM (Y 256 columns + two 128-column chunk accumulators = all
+// 512 columns) forces N = 128 for GEMM1 (three quarters of the N = 256 rate), three 32 KB operand stages deliver
+// ~57 B/clk, and the GELU chunks + LayerNorm tail keep the eight epilogue warps busy ~20 k of a tile's ~38 k clocks.
 #include <stdlib.h>
 
 #include "common.cuh"
