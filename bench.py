@@ -330,9 +330,10 @@ def run_b200(args):
         # launches of one kernel at one (M, N, K) are one entry, whatever their residual / output byte variant (rw)
         merged = {}
         for n, m, c, t in breakdown:
-            if n not in ("gemm_h16", "gemm_ln_h16"):
+            if n not in ("gemm_h16", "gemm_ln_h16", "ffn_ln_h16"):
                 continue
-            key = (n, m["M"], m["N"], m["K"])
+            # the fused feed-forward kernel is two chained GEMMs: N = d, K = F stands for both (flops 4 M d F)
+            key = (n, m["M"], m["N"], m["F"] if n == "ffn_ln_h16" else m["K"])
             c0_, t0_, b0_ = merged.get(key, (0, 0.0, 0.0))
             merged[key] = (c0_ + c, t0_ + t, b0_ + c * float(m.get("rw", 10)))
         gemm = sorted(((n, {"M": M_, "N": N_, "K": K_, "rw": b / c}, c, t) for (n, M_, N_, K_), (c, t, b) in merged.items()),
@@ -341,6 +342,10 @@ def run_b200(args):
             # algorithmic work per launch: 2MNK flops; bytes = A (16 bit) + outputs (+ fp32 residual for
             # the GEMM+LayerNorm kernel); the weights stay L2-resident and are not counted
             def algo(n, m):
+                if n == "ffn_ln_h16":
+                    # linear1 + linear2: 4 M d F flops; bytes = the residual pair in (it is also the A operand) and
+                    # the pair (or its hi half) out, m["rw"] per element; H never leaves the SM
+                    return 4.0 * m["M"] * m["N"] * m["K"], m["M"] * m["N"] * float(m["rw"])
                 fl = 2.0 * m["M"] * m["N"] * m["K"]
                 # GEMM+LN: fp32 residual in, fp32 + 16-bit out = 10 B per element; with the residual stream carried
                 # as a 16-bit (hi, lo) pair the wrapper records its own figure (m["rw"]: 4 in + 4 or 2 out)
@@ -353,8 +358,11 @@ def run_b200(args):
             fl0, by0 = algo(n0, m0)
             sec = t0 / c0 * 1e-3
             hbm_bound = by0 / (peaks["hbm_gbs"] * 1e9) > fl0 / (peaks["tflops_sustained"] * 1e12)
-            label = "%s M=%d N=%d K=%d" % ("gemm_ln_tcgen05_kernel" if n0 == "gemm_ln_h16" else "gemm_h16_tcgen05_kernel",
-                                           m0["M"], m0["N"], m0["K"])
+            if n0 == "ffn_ln_h16":
+                label = "ffn_ln_tcgen05_kernel M=%d d=%d F=%d" % (m0["M"], m0["N"], m0["K"])
+            else:
+                label = "%s M=%d N=%d K=%d" % ("gemm_ln_tcgen05_kernel" if n0 == "gemm_ln_h16"
+                                               else "gemm_h16_tcgen05_kernel", m0["M"], m0["N"], m0["K"])
             traffic = None
             tpath = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(tpath):

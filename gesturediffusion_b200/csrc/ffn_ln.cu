@@ -20,17 +20,18 @@
 // makes), so the LayerNorm tail only READS the accumulator in pass A and needs no residual loads.
 //
 // Roles (320 threads): warps 0..7 = epilogue (H chunks during the tile, then the LayerNorm tail of gemm_ln.cu:
-// pass A statistics, exchange by st.async, pass B normalise -> swizzled staging -> TMA stores of hi / lo; the two
-// staging blocks per warp are a dedicated 4 KB block and the warp's own slab of the locally produced H slot), warp 8 =
-// TMA producer (one ring of 32 KB stages: [X 128x64 | W1 128x64] for GEMM1, [W2 256x64] for GEMM2,
+// pass A statistics, exchange by st.async, pass B normalise -> swizzled staging -> TMA stores of hi / lo; the staging
+// block of a warp is its own slab of the locally produced H slot), warp 8 =
+// TMA producer (one ring of four 32 KB stages: [X 128x64 | W1 128x64] for GEMM1, [W2 256x64] for GEMM2,
 // [X_hi 128x64 | X_lo 128x64] for the residual, in exactly the order the MMA thread consumes them), warp 9 = UMMA
 // issuer.
 //
-// Status: parity-green and opt-in (GD_FUSE_FFN=1).  At d = 512, F = 1024, M = 25 216 it takes 75 us
-// against 77.5 us for gd_gemm_h16 (linear1 + GELU) + gd_gemm_h16_ln_split in the loop benchmark and gives the same
-// step time (inside the step graph the two-kernel path finds most of H still in L2).  The in-kernel timeline
+// Status: parity-green and the default feed-forward path (GD_FUSE_FFN=0 selects the two
+// kernels).  At d = 512, F = 1024, M = 25 216 it takes 69.5 us
+// against 79.5 us for gd_gemm_h16 (linear1 + GELU) + gd_gemm_h16_ln_split in the loop benchmark and makes the
+// cfg2a step 2-3 % shorter (1.497-1.529 vs 1.539-1.571 ms on the same boxes).  The in-kernel timeline
 // (gd_ffn_trace, tools/trace_ffn.py) shows the limits: TMEM (Y 256 columns + two 128-column chunk accumulators = all
-// 512 columns) forces N = 128 for GEMM1 (three quarters of the N = 256 rate), three 32 KB operand stages deliver
+// 512 columns) forces N = 128 for GEMM1 (three quarters of the N = 256 rate), four 32 KB operand stages deliver
 // ~57 B/clk, and the GELU chunks + LayerNorm tail keep the eight epilogue warps busy ~20 k of a tile's ~38 k clocks.
 #include <stdlib.h>
 
@@ -46,13 +47,17 @@ constexpr int kFfProducerWarp = kFfEpiWarps, kFfMmaWarp = kFfEpiWarps + 1;
 constexpr int kFfD = 512;                      // model width: K of GEMM1, N of GEMM2 (two CTAs x 256 columns)
 constexpr int kFfBN = 256;                     // output columns per CTA
 constexpr int kFfCH = 128;                     // hidden columns per chunk
-constexpr int kFfStages = 3;
+// Shared memory buys either a dedicated second staging block per epilogue warp (pass B never waits for the previous
+// chunk's store) or a fourth operand stage; the operand feed paces the tile, so it gets the memory:
+// 75.3 -> 69.5 us.
+constexpr bool kFfDedicatedLn = false;
+constexpr int kFfStages = kFfDedicatedLn ? 3 : 4;
 constexpr int kFfStageBytes = 32768;
 constexpr int kFfSlotBytes = 32768;            // one H chunk: two [128 rows x 64] 128B-swizzled K blocks
 constexpr int kFfRingOff = 0;
 constexpr int kFfHbufOff = kFfStages * kFfStageBytes;
 constexpr int kFfLnOff = kFfHbufOff + 2 * kFfSlotBytes;            // dedicated 4 KB block per epilogue warp
-constexpr int kFfI64Off = kFfLnOff + kFfEpiWarps * 4096;           // 64 x 64 identity, K-major 128B swizzle (8 KB)
+constexpr int kFfI64Off = kFfLnOff + (kFfDedicatedLn ? kFfEpiWarps * 4096 : 0);           // 64 x 64 identity, K-major 128B swizzle (8 KB)
 constexpr int kFfVecOff = kFfI64Off + 8192;                        // b2 | gamma | beta slices of this CTA
 constexpr int kFfStatOff = kFfVecOff + 3 * kFfBN * 4;              // [parity][part][row] (mean, M2)
 constexpr int kFfBarOff = kFfStatOff + 2 * 4 * kFfBM * 8;
@@ -351,7 +356,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     const uint32_t hfull_rem_peer = ptx::mapa(ptx::smem_u32(hfull_rem), rank ^ 1u);
     // LayerNorm tail: block 0 (dedicated) and block 1 (= the slab) stage the outputs of alternate column chunks
     const uint32_t blk0 = ptx::smem_u32(smem + kFfLnOff) + (uint32_t)ew * 4096u;
-    auto blk = [&](int c) { return (c & 1) ? slab : blk0; };
+    auto blk = [&](int c) { return (!kFfDedicatedLn || (c & 1)) ? slab : blk0; };
     const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;
     const uint32_t stats_s = ptx::smem_u32(smem + kFfStatOff);
     const uint32_t stats_cl[2] = {ptx::mapa(stats_s, rank), ptx::mapa(stats_s, rank ^ 1u)};
@@ -528,7 +533,10 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           v[4 * q + 2] = fmaf(fmaf(v[4 * q + 2] + b2.z, rstd, shift), g.z, b.z);
           v[4 * q + 3] = fmaf(fmaf(v[4 * q + 3] + b2.w, rstd, shift), g.w, b.w);
         }
-        if (lane == 0) ptx::bulk_wait_read_1();              // the store of chunk c - 2 has read this block
+        if (lane == 0) {                                     // the block's previous store has read it
+          if (kFfDedicatedLn) ptx::bulk_wait_read_1();
+          else ptx::bulk_wait_read_all();
+        }
         __syncwarp();
         const uint32_t sth = blk(c), stl = sth + 2048;
 #pragma unroll

@@ -104,9 +104,10 @@ class DenoiserEngine:
         self.fuse_ln = True            # GEMM + residual + LayerNorm in one kernel where gd_gemm_h16_ln supports d
         # residual stream between the fused kernels as a 16-bit (hi, lo) pair instead of fp32 (GD_SPLIT_RES=0: fp32)
         self.split_residual = os.environ.get("GD_SPLIT_RES", "1") != "0"
-        # linear1 + GELU + linear2 + residual + LayerNorm as ONE kernel (gd_ffn_h16_ln_split).  Opt-in: parity-green, but
-        # at d = 512 / F = 1024 it measures 86 us against 82 us for the two kernels it replaces
-        self.fuse_ffn = os.environ.get("GD_FUSE_FFN", "0") == "1"
+        # linear1 + GELU + linear2 + residual + LayerNorm as ONE kernel (gd_ffn_h16_ln_split) where it supports the shape
+        # (d = 512, F a multiple of 256): 69 us against 79.5 us for the two kernels it replaces at d = 512 / F = 1024, and
+        # H (M x F x 2 bytes per layer) never goes to HBM.  GD_FUSE_FFN=0 selects the two-kernel path.
+        self.fuse_ffn = os.environ.get("GD_FUSE_FFN", "1") == "1"
         # The encoder stack of the two guidance branches (or of two halves of the batch) as two independent kernel
         # chains on two streams: a persistent kernel's last, partly filled round of tiles (197 row tiles over 74
         # clusters = 2.66 -> 3 rounds at the cfg2a shapes) then overlaps the other chain's next kernel.

@@ -67,21 +67,21 @@ def test_forward_matches_oracle_fresh_inputs(cuda_device, arch, precision):
 @pytest.mark.parametrize("case", ["v1_humanml", "v2_gesture"])
 @pytest.mark.parametrize("precision", ["fp16", "bf16"])
 def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
-    """The opt-in one-kernel feed-forward sub-layer (gd_ffn_h16_ln_split, GD_FUSE_FFN=1) against the reference golden
-    and against the default two-kernel path."""
+    """The one-kernel feed-forward sub-layer (gd_ffn_h16_ln_split, the default; GD_FUSE_FFN=0 selects linear1 + GELU and
+    linear2 + residual + LayerNorm as two kernels) against the reference golden and against the two-kernel path."""
     cfg, sd, x, y, gold = load_model_case(case)
     m = build_product_model(cfg, sd, cuda_device, precision)
     xd, yd, t = x.to(cuda_device), to_dev(y, cuda_device), gold["t"].to(cuda_device)
-    base = m(xd, t, yd).clone()
+    fused = m(xd, t, yd).clone()
     eng = m.engine()
-    assert not eng.fuse_ffn
+    assert eng.fuse_ffn
     n0 = eng.kernels_per_step()
-    eng.fuse_ffn = True
+    eng.fuse_ffn = False
     try:
-        assert eng.kernels_per_step() == n0 - cfg["num_layers"]
-        fused = m(xd, t, yd)
+        assert eng.kernels_per_step() == n0 + cfg["num_layers"]
+        base = m(xd, t, yd).clone()
     finally:
-        eng.fuse_ffn = False
+        eng.fuse_ffn = True
     err = rel_l2(fused, gold["cond"])
     print("fused ffn %s %s: %.2e (vs two-kernel path %.2e)" % (case, precision, err, rel_l2(fused, base)))
     assert err < TOL[precision]
