@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "libgd_b200.so")
+# GD_B200_LIB: another build of the same library (A/B timing of two kernel versions on one box)
+LIB_PATH = os.environ.get("GD_B200_LIB") or os.path.join(_HERE, "_lib", "libgd_b200.so")
 
 GD_ACT_NONE, GD_ACT_GELU_ERF, GD_ACT_SILU = 0, 1, 2
 GD_F32, GD_BF16, GD_FP16 = 0, 1, 2

@@ -11,7 +11,10 @@
 //               pass 1: row max from TMEM; pass 2: p = exp2((s - max) * scale * log2e), row sum, P packed
 //               to 16 bit and written back to TMEM in place (cols [0, Sp/2)); after the PV MMA: O / sum ->
 //               16 bit -> swizzled smem staging -> row-contiguous 128-byte global stores.
-// Scores never touch shared or global memory; K/V are read once per item.  Numerics match the previous
+// Scores never touch shared or global memory; K/V are read once per item.  What bounds it (GD_ATT_DBG, DESIGN.md
+// 4.7): the per-item chain S -> softmax -> PV -> output with both TMEM slots in lockstep.  Tried and measured slower
+// on the same box: serving the slots as their barriers complete, half a cycle apart (30.6 vs 28.4 us), and
+// software-pipelined TMEM loads + four-way reductions in the softmax passes (31.7 vs 28.5 us).  Numerics match the previous
 // mma.sync kernel (fp32 scores / statistics, 16-bit P, fp32 accumulation).
 #include <stdlib.h>
 
@@ -29,6 +32,7 @@ constexpr int kAtSmemBytes = 2 * kAtQBytes + kAtKvRegion + kAtStgBytes + 256 + 1
 struct AtParams {
   void* out;
   int S, Sp, n_qt, H, d, n_items, fmt, rev;
+  int dbg;           // GD_ATT_DBG timing diagnostics (results wrong): 1 no Q/K/V loads, 2 no softmax arithmetic, 4 no stores
   float scale_log2e;
   uint32_t idesc_s, idesc_o;
 };
@@ -113,21 +117,33 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const int seq = item / p.H, head = item % p.H;
         const int row0 = seq * S, colq = head * 128;
         ptx::mbar_wait(&q_empty[slot], (use & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&q_full[slot], kAtQBytes);
         uint8_t* qs = q_smem + slot * kAtQBytes;
-        ptx::tma_load_2d(qs, &tmap_q, &q_full[slot], colq, row0 + qt * 128);
-        ptx::tma_load_2d(qs + 16384, &tmap_q, &q_full[slot], colq + 64, row0 + qt * 128);
+        if (p.dbg & 1) {
+          ptx::mbar_arrive(&q_full[slot]);
+        } else {
+          ptx::mbar_arrive_expect_tx(&q_full[slot], kAtQBytes);
+          ptx::tma_load_2d(qs, &tmap_q, &q_full[slot], colq, row0 + qt * 128);
+          ptx::tma_load_2d(qs + 16384, &tmap_q, &q_full[slot], colq + 64, row0 + qt * 128);
+        }
         if (last_of(u)) {                                   // after the item's last Q tile: its K and V
           uint8_t* ks = kv_smem + b * 2 * kv_bytes;
           uint8_t* vs = ks + kv_bytes;
           ptx::mbar_wait(&k_empty[b], (use & 1) ^ 1);
-          ptx::mbar_arrive_expect_tx(&k_full[b], kv_bytes);
-          ptx::tma_load_2d(ks, &tmap_kv, &k_full[b], p.d + colq, row0);
-          ptx::tma_load_2d(ks + slab, &tmap_kv, &k_full[b], p.d + colq + 64, row0);
+          if (p.dbg & 1) {
+            ptx::mbar_arrive(&k_full[b]);
+          } else {
+            ptx::mbar_arrive_expect_tx(&k_full[b], kv_bytes);
+            ptx::tma_load_2d(ks, &tmap_kv, &k_full[b], p.d + colq, row0);
+            ptx::tma_load_2d(ks + slab, &tmap_kv, &k_full[b], p.d + colq + 64, row0);
+          }
           ptx::mbar_wait(&v_empty[b], (use & 1) ^ 1);
-          ptx::mbar_arrive_expect_tx(&v_full[b], kv_bytes);
-          ptx::tma_load_2d(vs, &tmap_kv, &v_full[b], 2 * p.d + colq, row0);
-          ptx::tma_load_2d(vs + slab, &tmap_kv, &v_full[b], 2 * p.d + colq + 64, row0);
+          if (p.dbg & 1) {
+            ptx::mbar_arrive(&v_full[b]);
+          } else {
+            ptx::mbar_arrive_expect_tx(&v_full[b], kv_bytes);
+            ptx::tma_load_2d(vs, &tmap_kv, &v_full[b], 2 * p.d + colq, row0);
+            ptx::tma_load_2d(vs + slab, &tmap_kv, &v_full[b], 2 * p.d + colq + 64, row0);
+          }
         }
       }
     }
@@ -202,7 +218,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       ptx::tc_fence_after();
       // ---- pass 1: row maximum
       float mx = -INFINITY;
-      for (int c = 0; c < Sp; c += 32) {
+      for (int c = 0; c < ((p.dbg & 2) ? 0 : Sp); c += 32) {
         uint32_t r[32];
         const bool wide = c + 32 <= Sp;
         if (wide) {
@@ -226,7 +242,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       // ---- pass 2: probabilities -> TMEM (16-bit pairs, in place), row sum
       const float mb = -mx * sl2;
       float sum = 0.f;
-      for (int c = 0; c < Sp; c += 32) {
+      for (int c = 0; c < ((p.dbg & 2) ? 0 : Sp); c += 32) {
         uint32_t r[32];
         const bool wide = c + 32 <= Sp;
         if (wide) {
@@ -265,6 +281,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&p_ready[slot]);
+      if (p.dbg & 2) sum = 1.f;
       const float inv = 1.0f / sum;
 
       // ---- output: O / sum -> 16 bit -> staging -> row-contiguous stores
@@ -300,7 +317,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         for (int it = 0; it < 8; ++it) {
           const int rl = it * 4 + rsub, q = q_base + rl;
           const uint4 val = ptx::lds_v4u(stg + rl * 128 + ((j8 ^ (rl & 7)) << 4));
-          if (q < S)
+          if (q < S && !(p.dbg & 4))
             *reinterpret_cast<uint4*>(out + ((size_t)(seq * S + q) * p.d + head * 128 + h * 64 + j8 * 8)) = val;
         }
         __syncwarp();
@@ -354,6 +371,12 @@ int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_head
       rev = e ? atoi(e) : 1;
     }
     p.rev = rev;
+    static int dbg = -1;
+    if (dbg < 0) {
+      const char* e = getenv("GD_ATT_DBG");
+      dbg = e ? atoi(e) : 0;
+    }
+    p.dbg = dbg;
   }
   p.scale_log2e = (1.0f / sqrtf(128.0f)) * 1.4426950408889634f;
   p.idesc_s = ptx::umma_idesc_h16_f32(128, Sp, fmt == GD_FP16);
