@@ -108,6 +108,10 @@ class DenoiserEngine:
         # (d = 512, F a multiple of 256): 69 us against 79.5 us for the two kernels it replaces at d = 512 / F = 1024, and
         # H (M x F x 2 bytes per layer) never goes to HBM.  GD_FUSE_FFN=0 selects the two-kernel path.
         self.fuse_ffn = os.environ.get("GD_FUSE_FFN", "1") == "1"
+        # ... from this many token rows on: a cluster streams all of W1 and W2 per 128-row tile, so with few tiles (small
+        # batches) the two GEMM kernels, which spread N over the SMs, are faster (batch 1 x 196 frames: 0.40 vs 0.50 ms per
+        # denoise step; break-even near 25 row tiles, profiles/r01g_sweep.md)
+        self.fuse_ffn_min_rows = int(os.environ.get("GD_FUSE_FFN_MIN_ROWS", "4096"))
         # The encoder stack of the two guidance branches (or of two halves of the batch) as two independent kernel
         # chains on two streams: a persistent kernel's last, partly filled round of tiles (197 row tiles over 74
         # clusters = 2.66 -> 3 rounds at the cfg2a shapes) then overlaps the other chain's next kernel.
@@ -364,7 +368,7 @@ class DenoiserEngine:
                 res = dict(res_f32=X32) if l == 0 else dict(res_hi=Xa, res_lo=Xlo)
                 K.gemm_ln_split(ATT, w[p + "o.w"], w[p + "o.b"], w[p + "norm1.g"], w[p + "norm1.b"],
                                 out_hi=Xa, out_lo=Xlo, K=d, **res)
-                if self.fuse_ffn and K.ffn_ln_supported(Xa, d, self.F):
+                if self.fuse_ffn and r1 - r0 >= self.fuse_ffn_min_rows and K.ffn_ln_supported(Xa, d, self.F):
                     K.ffn_ln_split(Xa, Xlo, w[p + "f1.w"], w[p + "f1.b"], w[p + "f2.w"], w[p + "f2.b"],
                                    w[p + "norm2.g"], w[p + "norm2.b"], out_hi=Xa, out_lo=None if last else Xlo)
                     continue
@@ -387,12 +391,15 @@ class DenoiserEngine:
             K.gemm(Hh, w[p + "f2.w"], K.epilogue(bias=w[p + "f2.b"], residual=X32, out_f32=rows("Y32")), K=self.F)
             K.layernorm(rows("Y32"), w[p + "norm2.g"], w[p + "norm2.b"], out_f32=X32, out_h16=xa_b)
 
-    def kernels_per_step(self):
+    def kernels_per_step(self, rows):
+        """Kernel launches of one denoiser evaluation over `rows` token rows (nb * B * S)."""
+        split = self.split_streams and self.h16              # one chain per half of the sequences (n_seq >= 2)
         per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512)) else 7
-        if per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512 and self.F % 256 == 0:
+        if (per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512
+                and self.F % 256 == 0 and (rows // 2 if split else rows) >= self.fuse_ffn_min_rows):
             per_layer = 4
-        if self.split_streams and self.h16:
-            per_layer *= 2                                   # one chain per half of the sequences (n_seq >= 2)
+        if split:
+            per_layer *= 2
         return 2 + (1 if self.arch == "v2" else 0) + per_layer * self.L + 1
 
     def flops_per_step(self, B, T, nb):

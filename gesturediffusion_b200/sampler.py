@@ -159,7 +159,7 @@ class FastLoop:
                 if graph is not None:
                     graph.replay()
                     STATS["graph_replays"] += 1
-                    STATS["graph_kernels"] += self.launches_per_step()
+                    STATS["graph_kernels"] += self.launches_per_step(ws["R"])
                 else:
                     self._step(ws, st, tabs, flags, coef)
                 last = k == n_exec - 1
@@ -171,5 +171,5 @@ class FastLoop:
                 else:
                     yield None
 
-    def launches_per_step(self):
-        return self.engine.kernels_per_step() + 1
+    def launches_per_step(self, rows):
+        return self.engine.kernels_per_step(rows) + 1
