@@ -99,7 +99,12 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
   const uint64_t rng_sample = a.const_noise ? (uint64_t)a.sample_base : (uint64_t)(a.sample_base + b);
   const uint64_t rng_seed = a.seed_dev ? *a.seed_dev : a.seed;
   const int n = rows * T;                          // floats in this slab
-  const bool vec_ok = ((slab_off & 3) == 0) && ((noise_off & 3) == 0) && ((((size_t)j0 * T) & 3) == 0);
+  // float4 / uchar4 access needs the element offsets AND every base pointer 16-byte (mask: 4-byte) aligned: the
+  // guidance path passes uncond = OUT + B*J*T, which is only 4-byte aligned when B*J*T % 4 != 0 (odd T, B = 1 ...)
+  const uintptr_t bases = (uintptr_t)a.cond | (uintptr_t)a.uncond | (uintptr_t)a.x_t | (uintptr_t)a.noise |
+                          (uintptr_t)a.inpainted | (uintptr_t)a.x_prev | (uintptr_t)a.pred_xstart | (uintptr_t)a.mean;
+  const bool vec_ok = ((slab_off & 3) == 0) && ((noise_off & 3) == 0) && ((((size_t)j0 * T) & 3) == 0) &&
+                      ((bases & 15) == 0) && (((uintptr_t)a.inpaint_mask & 3) == 0);
   const int n4 = vec_ok ? (n >> 2) : 0;
 
   for (int i = threadIdx.x; i < n4; i += PS_THREADS) {

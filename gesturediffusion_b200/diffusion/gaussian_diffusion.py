@@ -6,8 +6,9 @@ coefficient tables of ``GaussianDiffusion.__init__`` (:120-199), ``q_sample`` (:
 ``q_posterior_mean_variance`` (:253-275), ``p_mean_variance`` (:277-388), ``p_sample`` (:496-548),
 ``p_sample_loop`` (:598-661) and ``p_sample_loop_progressive`` (:663-730).  The tables stay numpy
 float64 on the host (bit-identical formulas); all tensor arithmetic runs in the sm_100a kernels
-behind include/gd_b200.h.  Training losses, DDIM/PLMS and cond_fn guidance are out of scope and
-raise ``NotImplementedError`` instead of silently running something else.  There is no CPU path.
+behind include/gd_b200.h.  ``ddim_sample`` / ``ddim_sample_loop[_progressive]`` (:732-993) run through the
+same step graph with another coefficient table.  Training losses, PLMS and cond_fn guidance are out of
+scope and raise ``NotImplementedError`` instead of silently running something else.  There is no CPU path.
 """
 import enum
 import math
@@ -132,7 +133,12 @@ class GaussianDiffusion:
                     self.sqrt_recip_alphas_cumprod, self.sqrt_recipm1_alphas_cumprod, var]
             coef = th.from_numpy(np.stack(rows)).float().to(device).contiguous()
             tmap = getattr(self, "timestep_map", None) or list(range(self.num_timesteps))
+            import hashlib
+            sig = hashlib.sha1(np.ascontiguousarray(self.betas, dtype=np.float64).tobytes()
+                               + np.asarray(tmap, dtype=np.int64).tobytes()
+                               + repr((self.model_var_type, self.model_mean_type)).encode()).hexdigest()
             self._dev_cache[key] = dict(
+                sig=sig,                                   # schedule content: keys the captured step graphs (sampler.py)
                 coef=coef,
                 sqrt_acp=th.from_numpy(self.sqrt_alphas_cumprod).float().to(device),
                 sqrt_1macp=th.from_numpy(self.sqrt_one_minus_alphas_cumprod).float().to(device),

@@ -97,6 +97,8 @@ def gather_motions(local, batch, group=None):
         pad = torch.cat((local, local.new_zeros((mx - local.shape[0],) + tuple(local.shape[1:]))), dim=0)
     out = local.new_empty((world * mx,) + tuple(local.shape[1:]))
     dist.all_gather_into_tensor(out, pad.contiguous(), group=group)
+    if min(sizes) == mx:
+        return out                                   # equal shards: the collective's output already is the batch
     parts = [out[r * mx: r * mx + sizes[r]] for r in range(world)]
     return torch.cat(parts, dim=0)
 
@@ -109,8 +111,12 @@ def sharded_p_sample_loop(diffusion, model, shape, model_kwargs=None, noise=None
     world = dist.get_world_size() if dist.is_initialized() else 1
     device = next(model.parameters()).device
     loc_shape, loc_kwargs, loc_noise, base = shard_inputs(shape, model_kwargs, rank, world, noise)
-    diffusion.rng = "philox"
-    diffusion.seed = broadcast_seed(seed, device)
-    diffusion.sample_base = base
-    out = diffusion.p_sample_loop(model, loc_shape, noise=loc_noise, model_kwargs=loc_kwargs, **kwargs)
+    saved = (diffusion.rng, diffusion.seed, diffusion.sample_base)
+    try:
+        diffusion.rng = "philox"
+        diffusion.seed = broadcast_seed(seed, device)
+        diffusion.sample_base = base
+        out = diffusion.p_sample_loop(model, loc_shape, noise=loc_noise, model_kwargs=loc_kwargs, **kwargs)
+    finally:
+        diffusion.rng, diffusion.seed, diffusion.sample_base = saved     # the caller's diffusion object is unchanged
     return gather_motions(out, shape[0]) if gather else out

@@ -27,7 +27,7 @@ class ClassifierFreeSampleModel(nn.Module):
         B, J, F_, T = x.shape
         ws = eng.workspace(B, T, 2)
         with torch.no_grad():
-            eng.prepare_cond(ws, y, [False, True])
+            eng.prepare_cond(ws, y, [bool(y.get('uncond', False)), True])
             xin = x.to(eng.device, torch.float32).contiguous()
             eng.load_x(ws, xin)
             ws["t"].copy_(timesteps.to(eng.device).long())

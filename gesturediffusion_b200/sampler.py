@@ -19,6 +19,7 @@ from .diffusion.gaussian_diffusion import ModelMeanType
 # launch accounting for bench.py's `gpu_launches` claim: eager launches are counted by the library
 # (gd_launch_count); kernels replayed from a captured graph are counted here.
 STATS = {"graph_replays": 0, "graph_kernels": 0}
+MAX_GRAPHS_PER_STATE = 8
 
 
 def is_engine_model(model):
@@ -83,7 +84,8 @@ class FastLoop:
             raise ValueError("shape %s does not match the model's %d input features" % (shape, eng.J))
         y = model_kwargs.get("y", {}) if model_kwargs else {}
         nb = 2 if self.cfg else 1
-        branches = [False, True] if self.cfg else [bool(y.get("uncond", False))]
+        # cfg_sampler.py:23-28 passes y (with whatever y['uncond'] says) to the first call and forces uncond on the second
+        branches = [bool(y.get("uncond", False)), True] if self.cfg else [bool(y.get("uncond", False))]
         rng = "inject" if step_noise is not None else d.rng
         if rng not in ("torch", "philox", "inject"):
             raise ValueError("diffusion.rng must be 'torch' or 'philox'")
@@ -127,10 +129,17 @@ class FastLoop:
             flags = dict(clip=bool(clip_denoised), const_noise=bool(const_noise), ddim=ddim_eta is not None)
             # the Philox seed is read from device memory, so one captured graph serves every seed (chunked takes)
             st["seed"].fill_(int(d.seed) & 0x7FFFFFFFFFFFFFFF)
-            gkey = (flags["clip"], flags["const_noise"], d.model_mean_type, d.sample_base, flags["ddim"], id(coef))
+            # A captured graph bakes in the pointers of coef / timestep_map and n_steps: key it on the schedule CONTENT
+            # (not on object identity, which CPython reuses) and keep those tensors alive next to the graph.
+            gkey = (flags["clip"], flags["const_noise"], d.model_mean_type, d.sample_base, flags["ddim"], tabs["sig"],
+                    None if ddim_eta is None else float(ddim_eta))
             graph = None
             if d.use_cuda_graph:
-                graph = st["graphs"].get(gkey)
+                entry = st["graphs"].pop(gkey, None)
+                if entry is not None:
+                    graph, coef, tmap_keep = entry          # replay against the tensors the graph was captured with
+                    tabs = dict(tabs, timestep_map=tmap_keep)
+                    st["graphs"][gkey] = entry              # re-insert: most recently used last
                 if graph is None:
                     # warm-up run outside capture (sets kernel attributes, allocates nothing afterwards)
                     st["x"].copy_(img)
@@ -141,7 +150,9 @@ class FastLoop:
                     graph = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(graph):
                         self._step(ws, st, tabs, flags, coef)
-                    st["graphs"][gkey] = graph
+                    st["graphs"][gkey] = (graph, coef, tabs["timestep_map"])
+                    while len(st["graphs"]) > MAX_GRAPHS_PER_STATE:      # bounded: evict the least recently used
+                        st["graphs"].pop(next(iter(st["graphs"])))
 
             st["x"].copy_(img)
             eng.load_x(ws, st["x"])
