@@ -15,11 +15,34 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("GD_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "reference_path.zip")
+
+
+def _pick_root():
+    """/root/reference in the build container; on the GPU box (no /root/reference) the archive of byte-identical
+    copies of the same modules that oracle/stage_ref.py wrote to oracle/_ref/ (git-ignored, travels with the snapshot)."""
+    env = os.environ.get("GD_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/diffusion"):
+        return "/root/reference"
+    return _STAGED
+
+
+REF_ROOT = _pick_root()
 
 
 def reference_available():
+    if REF_ROOT.endswith(".zip"):
+        return os.path.isfile(REF_ROOT)            # zipimport: the archive itself is the sys.path entry
     return os.path.isdir(os.path.join(REF_ROOT, "diffusion"))
+
+
+def reference_kind():
+    """'live' (the reference tree itself), 'staged' (oracle/_ref archive) or None."""
+    if not reference_available():
+        return None
+    return "staged" if os.path.realpath(REF_ROOT) == os.path.realpath(_STAGED) else "live"
 
 
 _loaded = {}
