@@ -6,17 +6,23 @@
 
 Metric: motion frames/sec of classifier-free-guided DDPM sampling (and ms per denoise step).
 One bench "step" = one full `p_sample_loop` call (D denoise steps) over one batch of synthetic
-conditioning.  Workload at every N: BASELINE.json configs[1] per GPU -- MDM trans_enc (`MDM_Old`) d512 /
-8 layers / 4 heads, text-to-motion shape 263 x 196, batch 64 per GPU, CFG 2.5, random-init weights,
-synthetic conditioning; D = 50 respaced steps (the metric's "50-step CFG DDPM"); one extra
-1000-step call is timed and reported under "ddpm1000" (configs[1] quotes 1000 steps), a 50-step DDIM call under
-"ddim50" and, for the GENEA feature layout (--workload cfg3), a 4-chunk take under "take4".
-Weak scaling: per-GPU batch fixed, global batch = 64 * N, weights/seed broadcast once, motions
-all-gathered at the end of every call, no per-step collective.
+conditioning.  Headline workload at every N (kept from round 1 so rounds stay comparable): BASELINE.json
+configs[1] per GPU -- MDM trans_enc (`MDM_Old`) d512 / 8 layers / 4 heads, text-to-motion shape 263 x 196,
+batch 64 per GPU, CFG 2.5, random-init weights, synthetic conditioning; D = 50 respaced steps (the metric's
+"50-step CFG DDPM").  Weak scaling: per-GPU batch fixed, global batch = 64 * N, weights/seed broadcast once,
+motions all-gathered at the end of every call, no per-step collective.
 
-The JSON line carries: value (device-resident inputs), e2e (host pinned inputs -> H2D, result -> D2H inside
-the timed region), roofline (dominant kernel, CUDA-event timed in this process), cpu_baseline (the CPU oracle
-port on this box's cores, bounded sample), clocks (nvidia-smi during the timed region), gpu_launches.
+Extra keys of the same JSON line (each a full measurement of another BASELINE config, `--skip-extras` drops them):
+  cfg4      configs[3]: KIT 251 x 196, CFG, GLOBAL batch 1024 split over the N ranks (strong scaling), with the
+            start-up broadcast and the final gather timed separately
+  cfg3      configs[2]: the gesture model (V2: local attention + RoPE + encoder), 498 x 120, batch 128 per GPU
+  cfg2b     configs[1] as quoted: V2 with a 512-d text embedding, 263 x 200, batch 64, CFG, 1000-step DDPM
+  ddpm1000  the headline workload on the full 1000-step schedule;  ddim50 / take4: SURVEY 8.6 rows
+
+The JSON line carries: value (device-resident inputs), e2e (host pinned inputs -> H2D, every rank's shard of the
+result -> D2H inside the timed region), roofline (dominant kernel, CUDA-event timed in this process), cpu_baseline
+(the UNMODIFIED reference on this box's cores when oracle/_ref is staged, else the oracle port; bounded sample),
+clocks (nvidia-smi during the timed region), gpu_launches.
 """
 import argparse
 import json
@@ -34,11 +40,17 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     # name: (arch, njoints, frames, batch per GPU, use_text)
     "cfg2a": ("v1", 263, 196, 64, False),      # BASELINE configs[1] on the reference's runnable V1 path
+    "cfg2b": ("v2", 263, 200, 64, True),       # BASELINE configs[1] as quoted: V2 + 512-d text embedding (T 196 -> 200)
     "cfg3": ("v2", 498, 120, 128, False),      # BASELINE configs[2]: gesture model with local attention
-    "cfg4": ("v1", 251, 196, 128, False),      # BASELINE configs[3] per-GPU shard at 8 GPUs
+    "cfg4": ("v1", 251, 196, 128, False),      # BASELINE configs[3] per-GPU shard at 8 GPUs (global batch 1024)
     "cfg1": ("v1", 263, 196, 1, False),        # BASELINE configs[0] shape (B=1)
 }
+CFG4_GLOBAL_BATCH = 1024
 GUIDANCE = 2.5
+PRECISION_NOTE = ("16-bit mode = fp16 operands / fp32 accumulate (north_star names bf16): bf16's 8-bit mantissa gives "
+                  "3-4.5e-3 per-step rel-L2 by operand rounding alone (tools/sim_16bit_rounding.py), above the 2e-3 "
+                  "bound; fp16 measures 5-8e-4 at identical speed (same tcgen05 kind::f16 path); --precision bf16 runs "
+                  "the bf16 variant")
 
 
 def parse_args():
@@ -51,9 +63,11 @@ def parse_args():
     ap.add_argument("--denoise-steps", type=int, default=50)
     ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=0, help="override per-GPU batch")
+    ap.add_argument("--frames", type=int, default=0, help="override the number of frames")
     ap.add_argument("--no-cfg", action="store_true")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
-    ap.add_argument("--skip-1000", action="store_true")
+    ap.add_argument("--skip-extras", "--skip-1000", dest="skip_extras", action="store_true",
+                    help="headline workload only (no cfg4 / cfg3 / cfg2b / ddpm1000 / ddim / take legs)")
     ap.add_argument("--profile-out", default="", help="write the per-kernel CUDA-event breakdown to this JSON file")
     return ap.parse_args()
 
@@ -113,66 +127,107 @@ def measured_peaks():
     return dict(tflops_burst=1590.0, tflops_sustained=1400.0, hbm_gbs=6650.0, source="fallback (B200_PROFILING.md)")
 
 
-def build_case(args, device=None):
-    from gesturediffusion_b200.synthetic import make_inputs, make_state_dict, model_config
-    arch, J, T, B, use_text = WORKLOADS[args.workload]
-    if args.batch:
-        B = args.batch
+def build_case(workload, batch=0, frames=0):
+    from gesturediffusion_b200.synthetic import make_state_dict, model_config
+    arch, J, T, B, use_text = WORKLOADS[workload]
+    if batch:
+        B = batch
+    if frames:
+        T = frames
     cfg = model_config(arch=arch, njoints=J, use_text=use_text)
     sd = make_state_dict(cfg, seed=0)
     return cfg, sd, B, T
 
 
-def workload_name(args, cfg, B, T, D, use_cfg):
-    return ("%s: %s d%d L%d H%d, %dx%d, batch %d/GPU, %s, %d-step respaced DDPM (cosine, START_X, FIXED_SMALL)"
-            % (args.workload, "MDM_Old (V1 trans_enc)" if cfg["arch"] == "v1" else "MDM (V2 local-attn+RoPE+trans_enc)",
-               cfg["latent_dim"], cfg["num_layers"], cfg["num_heads"], cfg["njoints"], T, B,
-               "CFG %.1f" % GUIDANCE if use_cfg else "no CFG", D))
+def workload_name(workload, cfg, B, T, D, use_cfg):
+    return ("%s: %s d%d L%d H%d%s, %dx%d, batch %d/GPU, %s, %d-step respaced DDPM (cosine, START_X, FIXED_SMALL)"
+            % (workload, "MDM_Old (V1 trans_enc)" if cfg["arch"] == "v1" else "MDM (V2 local-attn+RoPE+trans_enc)",
+               cfg["latent_dim"], cfg["num_layers"], cfg["num_heads"], " +text" if cfg.get("use_text") else "",
+               cfg["njoints"], T, B, "CFG %.1f" % GUIDANCE if use_cfg else "no CFG", D))
 
 
-# ------------------------------------------------------------------------------------------ CPU oracle timing
-def cpu_oracle_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads, min_seconds=12.0):
-    """Times the CPU oracle port (oracle/: the reference's algorithm restated on torch CPU ops, pinned to the
-    reference by tests/golden) on a bounded sample; returns (frames/s for a D-step chain, ms/denoise-step,
-    description).  Linear extrapolation in batch and steps is stated in the description."""
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads, min_seconds=12.0):
+    """Times the reference's CPU implementation of the path on a bounded sample: the UNMODIFIED reference
+    (`SpacedDiffusion.p_sample_loop` over `MDM` / `MDM_Old` under `ClassifierFreeSampleModel`, fp32, CPU) when it
+    is available -- /root/reference in the build container, the byte-identical archive oracle/_ref/ that
+    oracle/stage_ref.py staged on the GPU box -- (kind 'reference'), else the oracle port (kind 'port').
+    Returns (frames/s for a D-step chain, ms per denoise step, kind, description).  The sample runs the LAST
+    `sample_steps` of the D-step schedule (every step costs the same); frames/s = batch*frames / (ms * D)."""
     from gesturediffusion_b200.synthetic import make_inputs, make_step_noise
-    from oracle.diffusion_oracle import OracleDiffusion, oracle_cfg
-    from oracle.model_oracle import make_model_fn
     torch.set_num_threads(threads)
-    fn = make_model_fn(sd, cfg)
-    model = oracle_cfg(fn) if use_cfg else fn
-    od = OracleDiffusion(respacing=[D])
     x, y = make_inputs(cfg, sample_b, T, guidance=GUIDANCE)
-    noises = make_step_noise(tuple(x.shape), sample_steps)
-    od.p_sample_loop(model, x, y, noises[:1], skip_timesteps=D - 1)           # warm-up: one step
+    kind = "port"
+    try:
+        from oracle import ref_shims
+        if ref_shims.reference_available():
+            kind = "reference"
+    except Exception:                                   # noqa: BLE001 -- any import problem -> the port
+        kind = "port"
+    if kind == "reference":
+        ns = ref_shims.load_reference()
+        net = ref_shims.build_reference_model(cfg["arch"], cfg["njoints"], latent_dim=cfg["latent_dim"],
+                                              num_layers=cfg["num_layers"], num_heads=cfg["num_heads"],
+                                              ff_size=cfg["ff_size"], seed_poses=cfg["seed_poses"],
+                                              use_text=cfg["use_text"])
+        missing, unexpected = net.load_state_dict(sd, strict=False)
+        assert not missing and not unexpected
+        model = ns.ClassifierFreeSampleModel(net) if use_cfg else net
+        dif = ref_shims.build_reference_diffusion([D])
+
+        def run(n_steps):
+            with torch.no_grad():
+                dif.p_sample_loop(model, tuple(x.shape), noise=x, clip_denoised=False, model_kwargs={"y": dict(y)},
+                                  skip_timesteps=D - n_steps, init_image=None, progress=False, dump_steps=None,
+                                  const_noise=False)
+        what = "unmodified reference (%s, torch CPU fp32, %d threads)" % (ref_shims.reference_kind(), threads)
+    else:
+        from oracle.diffusion_oracle import OracleDiffusion, oracle_cfg
+        from oracle.model_oracle import make_model_fn
+        fn = make_model_fn(sd, cfg)
+        model = oracle_cfg(fn) if use_cfg else fn
+        od = OracleDiffusion(respacing=[D])
+        noises = make_step_noise(tuple(x.shape), sample_steps)
+
+        def run(n_steps):
+            od.p_sample_loop(model, x, y, noises[:n_steps], skip_timesteps=D - n_steps)
+        what = "oracle port (torch CPU fp32, %d threads)" % threads
+    run(1)                                                                     # warm-up: one step
     reps, dt = 0, 0.0
     while dt < min_seconds or reps == 0:                                       # bounded sample: >= min_seconds of CPU work
         t0 = time.perf_counter()
-        od.p_sample_loop(model, x, y, noises, skip_timesteps=D - sample_steps)
+        run(sample_steps)
         dt += time.perf_counter() - t0
         reps += 1
     ms_step = dt / (reps * sample_steps) * 1e3
     fps = sample_b * T / (ms_step * 1e-3 * D)
-    desc = ("oracle port (torch CPU fp32, %d threads), batch %d x %d denoise steps x %d repeats timed (%.1f s), %s; "
+    desc = ("%s, batch %d x %d denoise steps x %d repeats timed (%.1f s), %s; "
             "frames/s = batch*frames / (ms_per_denoise_step * %d steps)"
-            % (threads, sample_b, sample_steps, reps, dt, "CFG" if use_cfg else "no CFG", D))
-    return fps, ms_step, desc
+            % (what, sample_b, sample_steps, reps, dt, "CFG" if use_cfg else "no CFG", D))
+    return fps, ms_step, kind, desc
+
+
+def cpu_sample_plan(B, D):
+    """Bounded CPU sample: the bench batch itself (up to 64) x a few of the D steps."""
+    if B <= 1:
+        return 1, D
+    return min(B, 64), 2
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on this box's host cores.  The
-    reference is Python and does not travel to the GPU box, so this is the oracle port (kind 'port')."""
+    """--impl reference: the reference's own CPU implementation of the path on this box's host cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cfg, sd, B, T = build_case(args)
+    cfg, sd, B, T = build_case(args.workload, args.batch, args.frames)
     D = args.denoise_steps
     use_cfg = not args.no_cfg
     threads = os.cpu_count() or 1
-    sample_b, sample_steps = (min(B, 16), 10) if B > 1 else (1, D)
+    sample_b, sample_steps = cpu_sample_plan(B, D)
     vals, ms = [], []
+    kind, desc = "port", ""
     for i in range(args.warmup + args.steps):
-        fps, ms_step, desc = cpu_oracle_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads)
+        fps, ms_step, kind, desc = cpu_rate(cfg, sd, T, D, use_cfg, sample_b, sample_steps, threads, min_seconds=6.0)
         if i >= args.warmup:
             vals.append(fps)
             ms.append(ms_step)
@@ -181,250 +236,8 @@ def run_reference(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": sum(ms) / len(ms) * D, "ms_per_denoise_step": sum(ms) / len(ms),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args, cfg, B, T, D, use_cfg), "denoise_steps": D,
+            "config": {"workload": workload_name(args.workload, cfg, B, T, D, use_cfg), "denoise_steps": D,
                        "parallelism": "cpu"},
-            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port", "sample": desc},
+            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind, "sample": desc},
             "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
-
-
-# ------------------------------------------------------------------------------------------ B200 arm
-def run_b200(args):
-    import torch.distributed as dist
-    from gesturediffusion_b200 import ClassifierFreeSampleModel, _cabi, create_gaussian_diffusion
-    from gesturediffusion_b200 import dist as gdist
-    from gesturediffusion_b200 import kernels as K
-    from gesturediffusion_b200 import sampler as S
-    from gesturediffusion_b200.synthetic import make_inputs
-
-    rank, world = gdist.init_process_group()
-    if world != args.gpus:
-        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch N>1 under torch.distributed.run)" % (args.gpus, world))
-    local = int(os.environ.get("LOCAL_RANK", rank))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    _cabi.load()                                     # fail loudly if the CUDA library is missing
-
-    cfg, sd, B, T = build_case(args)
-    D = args.denoise_steps
-    use_cfg = not args.no_cfg
-    J = cfg["njoints"]
-
-    # model: rank 0's weights are the job's weights (broadcast of the packed arenas), seed broadcast
-    from gesturediffusion_b200.synthetic import build_model
-    denoiser = build_model(cfg, sd, dev, args.precision)
-    eng = denoiser.engine()
-    gdist.broadcast_engine(eng, src=0)
-    model = ClassifierFreeSampleModel(denoiser) if use_cfg else denoiser
-    dif = create_gaussian_diffusion(timestep_respacing=[D])
-    dif.rng = "philox"
-    dif.seed = gdist.broadcast_seed(20261104, dev)
-    dif.sample_base = rank * B
-    shape = (B, J, 1, T)
-
-    # synthetic conditioning: pinned host copies (e2e) and device-resident copies (value)
-    _, y_host = make_inputs(cfg, B, T, seed=1234 + rank, guidance=GUIDANCE)
-    y_pin = {k: v.pin_memory() for k, v in y_host.items()}
-    y_dev = {k: v.to(dev) for k, v in y_host.items()}
-    out_pin = torch.empty(B * world if world > 1 else B, J, 1, T).pin_memory()
-    h2d = sum(v.numel() * v.element_size() for v in y_pin.values())
-    d2h = out_pin.numel() * 4
-
-    def one_call(e2e, diffusion=dif, skip=0):
-        if e2e:
-            y = {k: v.to(dev, non_blocking=True) for k, v in y_pin.items()}
-        else:
-            y = y_dev
-        out = diffusion.p_sample_loop(model, shape, clip_denoised=False, model_kwargs={"y": y}, skip_timesteps=skip)
-        if world > 1:
-            out = gdist.gather_motions(out, B * world)
-        if e2e:
-            out_pin.copy_(out, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-        return out
-
-    def timed(n, e2e, diffusion=dif):
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(n):
-            one_call(e2e, diffusion)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.barrier()
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
-
-    for _ in range(max(args.warmup, 3)):
-        one_call(False)
-    one_call(True)
-
-    sampler = ClockSampler(local) if rank == 0 else None
-    if sampler:
-        sampler.start()
-    l0 = _cabi.launch_count() + S.STATS["graph_kernels"]
-    ms_total = timed(args.steps, False)
-    launches = _cabi.launch_count() + S.STATS["graph_kernels"] - l0
-    ms_e2e = timed(args.steps, True)
-    clocks = sampler.stop() if sampler else None
-
-    frames = B * world * T * args.steps
-    value = frames / (ms_total * 1e-3)
-    ms_step = ms_total / args.steps
-    e2e_value = frames / (ms_e2e * 1e-3)
-
-    extra = {}
-    if not args.skip_1000:
-        dif1000 = create_gaussian_diffusion(timestep_respacing="")
-        dif1000.rng, dif1000.seed, dif1000.sample_base = "philox", dif.seed, dif.sample_base
-        one_call(False, dif1000, skip=990)                     # builds this schedule's step graph (10 steps)
-        ms1000 = timed(1, False, dif1000)
-        extra["ddpm1000"] = {"value": B * world * T / (ms1000 * 1e-3), "unit": "frames/s",
-                             "ms_per_denoise_step": ms1000 / 1000.0, "calls": 1}
-
-    # SURVEY 8.6 rows on the same workload, rank-local (no gather): 50-step DDIM (eta 0) and, for the 6-interleaved
-    # GENEA layout (cfg3), a 4-chunk take through generate_take (seed hand-off + de-normalise/split on the device)
-    if not args.skip_1000:
-        def timed_local(fn):
-            fn()
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            fn()
-            e1.record()
-            torch.cuda.synchronize()
-            return e0.elapsed_time(e1)
-        dif_ddim = create_gaussian_diffusion(timestep_respacing="ddim%d" % D)
-        dif_ddim.rng, dif_ddim.seed, dif_ddim.sample_base = "philox", dif.seed, dif.sample_base
-        ms_ddim = timed_local(lambda: dif_ddim.ddim_sample_loop(model, shape, clip_denoised=False,
-                                                                model_kwargs={"y": y_dev}, eta=0.0))
-        extra["ddim%d" % D] = {"value": B * T / (ms_ddim * 1e-3), "unit": "frames/s per GPU",
-                               "ms_per_denoise_step": ms_ddim / D}
-        if J % 6 == 0 and use_cfg:
-            from gesturediffusion_b200.generate import generate_take
-            chunks = [y_dev] * 4
-            mean, std = torch.zeros(J, device=dev), torch.ones(J, device=dev)
-            ms_take = timed_local(lambda: generate_take(model, dif, chunks, B, T, seed_poses=cfg["seed_poses"],
-                                                        guidance_param=GUIDANCE, mean=mean, std=std))
-            extra["take4"] = {"value": 4 * B * T / (ms_take * 1e-3), "unit": "frames/s per GPU", "chunks": 4,
-                              "ms_per_denoise_step": ms_take / (4 * D)}
-
-    # ---- roofline of the dominant kernel: CUDA events around every launch of one eager denoise pass
-    peaks = measured_peaks()
-    roof, breakdown = None, None
-    if rank == 0:
-        dif.use_cuda_graph = False
-        dif_p = create_gaussian_diffusion(timestep_respacing=[D])
-        dif_p.rng, dif_p.seed, dif_p.use_cuda_graph = "philox", dif.seed, False
-        K.PROFILE = []
-        dif_p.p_sample_loop(model, shape, clip_denoised=False, model_kwargs={"y": y_dev}, skip_timesteps=D - 6)
-        summ = K.profile_summary(K.PROFILE)
-        K.PROFILE = None
-        dif.use_cuda_graph = True
-        tot = sum(t for _, t in summ.values())
-        breakdown = sorted(((n, dict(m), c, t) for (n, m), (c, t) in summ.items()), key=lambda r: -r[3])
-        # launches of one kernel at one (M, N, K) are one entry, whatever their residual / output byte variant (rw)
-        merged = {}
-        for n, m, c, t in breakdown:
-            if n not in ("gemm_h16", "gemm_ln_h16", "ffn_ln_h16"):
-                continue
-            # the fused feed-forward kernel is two chained GEMMs: N = d, K = F stands for both (flops 4 M d F)
-            key = (n, m["M"], m["N"], m["F"] if n == "ffn_ln_h16" else m["K"])
-            c0_, t0_, b0_ = merged.get(key, (0, 0.0, 0.0))
-            merged[key] = (c0_ + c, t0_ + t, b0_ + c * float(m.get("rw", 10)))
-        gemm = sorted(((n, {"M": M_, "N": N_, "K": K_, "rw": b / c}, c, t) for (n, M_, N_, K_), (c, t, b) in merged.items()),
-                      key=lambda r: -r[3])
-        if gemm:
-            # algorithmic work per launch: 2MNK flops; bytes = A (16 bit) + outputs (+ fp32 residual for
-            # the GEMM+LayerNorm kernel); the weights stay L2-resident and are not counted
-            def algo(n, m):
-                if n == "ffn_ln_h16":
-                    # linear1 + linear2: 4 M d F flops; bytes = the residual pair in (it is also the A operand) and
-                    # the pair (or its hi half) out, m["rw"] per element; H never leaves the SM
-                    return 4.0 * m["M"] * m["N"] * m["K"], m["M"] * m["N"] * float(m["rw"])
-                fl = 2.0 * m["M"] * m["N"] * m["K"]
-                # GEMM+LN: fp32 residual in, fp32 + 16-bit out = 10 B per element; with the residual stream carried
-                # as a 16-bit (hi, lo) pair the wrapper records its own figure (m["rw"]: 4 in + 4 or 2 out)
-                by = m["M"] * m["K"] * 2.0 + (m["M"] * m["N"] * float(m.get("rw", 10)) if n == "gemm_ln_h16"
-                                              else m["M"] * m["N"] * 2.0)
-                return fl, by
-            fl_all = sum(algo(n, m)[0] * c for n, m, c, t in gemm)
-            tt = sum(t for n, m, c, t in gemm)
-            n0, m0, c0, t0 = gemm[0]                           # the kernel with the largest share of the step
-            fl0, by0 = algo(n0, m0)
-            sec = t0 / c0 * 1e-3
-            hbm_bound = by0 / (peaks["hbm_gbs"] * 1e9) > fl0 / (peaks["tflops_sustained"] * 1e12)
-            if n0 == "ffn_ln_h16":
-                label = "ffn_ln_tcgen05_kernel M=%d d=%d F=%d" % (m0["M"], m0["N"], m0["K"])
-            else:
-                label = "%s M=%d N=%d K=%d" % ("gemm_ln_tcgen05_kernel" if n0 == "gemm_ln_h16"
-                                               else "gemm_h16_tcgen05_kernel", m0["M"], m0["N"], m0["K"])
-            traffic = None
-            tpath = os.path.join(ROOT, "profiles", "traffic.json")
-            if os.path.exists(tpath):
-                traffic = json.load(open(tpath)).get(label, {}).get("dram_bytes_per_launch")
-            if hbm_bound:
-                ach, peak, unit = by0 / sec / 1e9, peaks["hbm_gbs"], "GB/s"
-            else:
-                ach, peak, unit = fl0 / sec / 1e12, peaks["tflops_sustained"], "TFLOP/s"
-            roof = {"bound": "hbm" if hbm_bound else "tensor", "kernel": label, "achieved": ach, "peak": peak,
-                    "unit": unit, "frac": ach / peak, "traffic": traffic, "peak_source": peaks["source"],
-                    "launch_ms": t0 / c0, "share_of_step": t0 / tot, "algorithmic_bytes_per_launch": by0,
-                    "algorithmic_flops_per_launch": fl0,
-                    "tensor_tflops_same_kernel": fl0 / sec / 1e12,
-                    "all_gemms": {"achieved": fl_all / (tt * 1e-3) / 1e12, "unit": "TFLOP/s",
-                                  "frac_of_tensor_peak": fl_all / (tt * 1e-3) / 1e12 / peaks["tflops_sustained"],
-                                  "share_of_step": tt / tot}}
-        if args.profile_out:
-            with open(args.profile_out, "w") as fh:
-                json.dump({"workload": workload_name(args, cfg, B, T, D, use_cfg), "eager_denoise_steps": 6,
-                           "total_ms": tot, "kernels": [{"name": n, "meta": m, "launches": c, "total_ms": t,
-                                                         "share": t / tot} for n, m, c, t in breakdown]}, fh, indent=1)
-
-    if rank != 0:
-        return
-    flops_step = eng.flops_per_step(B, T, 2 if use_cfg else 1)
-    step_tflops = flops_step / (ms_step / D * 1e-3) / 1e12
-    line = {"metric": "motion frames/sec (CFG DDPM sampling)", "value": value, "unit": "frames/s",
-            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
-            "ms_per_denoise_step": ms_step / D, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": {"fp16": "f16 operands / f32 accumulate", "bf16": "bf16 operands / f32 accumulate",
-                      "fp32": "f32"}[args.precision],
-            "data": "synthetic (random-init weights of the reference architecture, N(0,1) seed poses / MFCC)",
-            "config": {"workload": workload_name(args, cfg, B, T, D, use_cfg), "global_batch": B * world,
-                       "frames": T, "denoise_steps": D, "guidance": GUIDANCE if use_cfg else None,
-                       "parallelism": "dp%d (batch-sharded, no per-step collective)" % world,
-                       "noise": "in-kernel Philox4x32-10 keyed by (seed, global sample, step)",
-                       "l2": "per-denoise-step working set ~%d MB of activations > 126 MB L2; weights (%d MB) stay "
-                             "L2-resident as in production" % (2 * B * (T + 1) * 12 * cfg["latent_dim"] * 2 // 2 ** 20,
-                                                               sum(a.numel() * a.element_size() for a in eng.arenas.values()) // 2 ** 20)},
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": int(launches),
-            "step_roofline": {"bound": "tensor", "achieved": step_tflops, "peak": peaks["tflops_sustained"],
-                              "unit": "TFLOP/s", "frac": step_tflops / peaks["tflops_sustained"],
-                              "algorithmic_gflop_per_denoise_step": flops_step / 1e9},
-            "roofline": roof, "clocks": clocks}
-    line.update(extra)
-    if world == 1 and not args.skip_cpu_baseline:
-        threads = os.cpu_count() or 1
-        sb, ss = (min(B, 16), 10) if B > 1 else (1, D)
-        fps, ms_c, desc = cpu_oracle_rate(cfg, sd, T, D, use_cfg, sb, ss, threads)
-        line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": desc,
-                                "ms_per_denoise_step_at_sample_batch": ms_c}
-    print(json.dumps(line))
-
-
-if __name__ == "__main__":
-    a = parse_args()
-    if a.impl == "reference":
-        run_reference(a)
-    else:
-        run_b200(a)
-        import torch.distributed as _dist
-        if _dist.is_available() and _dist.is_initialized():
-            _dist.destroy_process_group()
