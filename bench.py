@@ -241,3 +241,131 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind, "sample": desc},
             "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------ B200 arm
+class Case:
+    """One workload on this rank: model + engine (weights broadcast from rank 0), diffusion schedule, synthetic
+    conditioning as pinned host tensors (e2e) and device tensors (value), and the timed-call helpers."""
+
+    def __init__(self, workload, B, T, D, precision, use_cfg, rank, world, dev, sample_base, seed, cfg_sd=None):
+        import torch.distributed as dist
+        from gesturediffusion_b200 import ClassifierFreeSampleModel, create_gaussian_diffusion
+        from gesturediffusion_b200 import dist as gdist
+        from gesturediffusion_b200.synthetic import build_model, make_inputs
+        self.dist, self.gdist = dist, gdist
+        self.workload, self.B, self.T, self.D = workload, B, T, D
+        self.rank, self.world, self.dev, self.use_cfg = rank, world, dev, use_cfg
+        self.cfg, self.sd = cfg_sd if cfg_sd else build_case(workload)[:2]
+        self.J = self.cfg["njoints"]
+        self.denoiser = build_model(self.cfg, self.sd, dev, precision)
+        self.eng = self.denoiser.engine()
+        # start-up collectives, timed once: rank 0's packed weight arenas (one broadcast per dtype) + the noise seed
+        self._sync()
+        t0 = time.perf_counter()
+        gdist.broadcast_engine(self.eng, src=0)
+        self.seed = gdist.broadcast_seed(seed, dev)
+        self._sync()
+        self.broadcast_ms = (time.perf_counter() - t0) * 1e3
+        self.model = ClassifierFreeSampleModel(self.denoiser) if use_cfg else self.denoiser
+        self.make_dif = lambda resp: self._dif(create_gaussian_diffusion(timestep_respacing=resp), sample_base)
+        self.dif = self.make_dif([D])
+        self.shape = (B, self.J, 1, T)
+        self.global_batch = None                      # set by the caller (weak: B * world, strong: fixed)
+        _, y_host = make_inputs(self.cfg, B, T, seed=1234 + sample_base, guidance=GUIDANCE)
+        self.y_pin = {k: v.pin_memory() for k, v in y_host.items()}
+        self.y_dev = {k: v.to(dev) for k, v in y_host.items()}
+        self.out_pin = torch.empty(B, self.J, 1, T).pin_memory()         # this rank's shard of the motions
+        self.h2d = sum(v.numel() * v.element_size() for v in self.y_pin.values())
+        self.d2h = self.out_pin.numel() * 4
+
+    def _dif(self, dif, sample_base):
+        dif.rng, dif.seed, dif.sample_base = "philox", self.seed, sample_base
+        return dif
+
+    def _sync(self):
+        torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+
+    def one_call(self, e2e, diffusion=None, skip=0):
+        """value path: conditioning resident in HBM, motions all-gathered on the device (every rank holds the batch).
+        e2e path: conditioning H2D from pinned memory, and every rank copies ITS OWN shard of the motions to its pinned
+        host buffer (one PCIe link per GPU in parallel; no rank moves another rank's shard to the host)."""
+        dif = diffusion or self.dif
+        y = {k: v.to(self.dev, non_blocking=True) for k, v in self.y_pin.items()} if e2e else self.y_dev
+        out = dif.p_sample_loop(self.model, self.shape, clip_denoised=False, model_kwargs={"y": y}, skip_timesteps=skip)
+        if e2e:
+            self.out_pin.copy_(out, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        elif self.world > 1:
+            out = self.gdist.gather_motions(out, self.global_batch)
+        return out
+
+    def timed(self, n, e2e, diffusion=None):
+        """CUDA events around n calls, barrier + synchronize on both sides, max over ranks (ms)."""
+        self._sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            self.one_call(e2e, diffusion)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=self.dev)
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.all_reduce(ms, op=self.dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def timed_gather(self, reps=5):
+        """The final all-gather alone (ms per call, max over ranks)."""
+        if self.world == 1:
+            return 0.0
+        x = torch.zeros(self.shape, device=self.dev)
+        self.gdist.gather_motions(x, self.global_batch)
+        self._sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            self.gdist.gather_motions(x, self.global_batch)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / reps], device=self.dev)
+        self.dist.all_reduce(ms, op=self.dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def free(self):
+        self.eng._ws.clear()
+        self.denoiser = self.model = self.eng = self.dif = None
+        torch.cuda.empty_cache()
+
+
+def extra_case(workload, B, T, D, args, rank, world, dev, sample_base, global_batch, steps, peaks, respacing=None):
+    """One more BASELINE config measured like the headline (value + e2e + step roofline); returns its JSON object."""
+    cfg, sd, _, _ = build_case(workload)
+    c = Case(workload, B, T, D, args.precision, True, rank, world, dev, sample_base, 20261104, cfg_sd=(cfg, sd))
+    c.global_batch = global_batch
+    dif = c.make_dif(respacing) if respacing is not None else c.dif
+    n_den = dif.num_timesteps
+    if n_den > 100:
+        c.one_call(False, dif, skip=n_den - 10)               # builds the step graph of this schedule (10 steps)
+    else:
+        for _ in range(2):
+            c.one_call(False, dif)
+    c.one_call(True, dif, skip=max(n_den - 10, 0))
+    ms = c.timed(steps, False, dif) / steps
+    ms_e2e = c.timed(steps, True, dif) / steps
+    frames = global_batch * T
+    flops = c.eng.flops_per_step(B, T, 2)
+    tf = flops / (ms / n_den * 1e-3) / 1e12
+    obj = {"workload": workload_name(workload, cfg, B, T, n_den, True), "global_batch": global_batch,
+           "per_gpu_batch": B, "value": frames / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms,
+           "ms_per_denoise_step": ms / n_den, "calls_timed": steps,
+           "e2e": {"value": frames / (ms_e2e * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": c.h2d * world,
+                   "d2h_bytes_per_step": c.d2h * world, "ms_per_step": ms_e2e},
+           "broadcast_ms": c.broadcast_ms, "gather_ms": c.timed_gather(),
+           "step_roofline": {"bound": "tensor", "achieved": tf, "peak": peaks["tflops_sustained"], "unit": "TFLOP/s",
+                             "frac": tf / peaks["tflops_sustained"],
+                             "algorithmic_gflop_per_denoise_step_per_gpu": flops / 1e9}}
+    c.free()
+    return obj
