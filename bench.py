@@ -369,3 +369,81 @@ def extra_case(workload, B, T, D, args, rank, world, dev, sample_base, global_ba
                              "algorithmic_gflop_per_denoise_step_per_gpu": flops / 1e9}}
     c.free()
     return obj
+
+
+def dominant_kernel_roofline(c, peaks, profile_out):
+    """CUDA events around every launch of six eager denoise steps of the headline workload: per-kernel breakdown and the
+    roofline of the kernel with the largest share of the step (rank 0)."""
+    from gesturediffusion_b200 import kernels as K
+    D = c.D
+    dif_p = c.make_dif([D])
+    dif_p.use_cuda_graph = False
+    K.PROFILE = []
+    dif_p.p_sample_loop(c.model, c.shape, clip_denoised=False, model_kwargs={"y": c.y_dev}, skip_timesteps=D - 6)
+    summ = K.profile_summary(K.PROFILE)
+    K.PROFILE = None
+    tot = sum(t for _, t in summ.values())
+    breakdown = sorted(((n, dict(m), cnt, t) for (n, m), (cnt, t) in summ.items()), key=lambda r: -r[3])
+    # launches of one kernel at one (M, N, K) are one entry, whatever their residual / output byte variant (rw)
+    merged = {}
+    for n, m, cnt, t in breakdown:
+        if n not in ("gemm_h16", "gemm_ln_h16", "ffn_ln_h16"):
+            continue
+        # the fused feed-forward kernel is two chained GEMMs: N = d, K = F stands for both (flops 4 M d F)
+        key = (n, m["M"], m["N"], m["F"] if n == "ffn_ln_h16" else m["K"])
+        c0_, t0_, b0_ = merged.get(key, (0, 0.0, 0.0))
+        merged[key] = (c0_ + cnt, t0_ + t, b0_ + cnt * float(m.get("rw", 10)))
+    gemm = sorted(((n, {"M": M_, "N": N_, "K": K_, "rw": b / cnt}, cnt, t) for (n, M_, N_, K_), (cnt, t, b) in merged.items()),
+                  key=lambda r: -r[3])
+    roof = None
+    if gemm:
+        # algorithmic work per launch (DESIGN.md 4): 2MNK flops; bytes = A (16 bit) + outputs (+ the residual pair for
+        # the GEMM+LayerNorm kernels); the weights stay L2-resident and are not counted
+        def algo(n, m):
+            if n == "ffn_ln_h16":
+                # linear1 + linear2: 4 M d F flops; bytes = the residual pair in (it is also the A operand) and
+                # the pair (or its hi half) out, m["rw"] per element; H never leaves the SM
+                return 4.0 * m["M"] * m["N"] * m["K"], m["M"] * m["N"] * float(m["rw"])
+            fl = 2.0 * m["M"] * m["N"] * m["K"]
+            by = m["M"] * m["K"] * 2.0 + (m["M"] * m["N"] * float(m.get("rw", 10)) if n == "gemm_ln_h16"
+                                          else m["M"] * m["N"] * 2.0)
+            return fl, by
+        fl_all = sum(algo(n, m)[0] * cnt for n, m, cnt, t in gemm)
+        tt = sum(t for n, m, cnt, t in gemm)
+        n0, m0, c0, t0 = gemm[0]                           # the kernel with the largest share of the step
+        fl0, by0 = algo(n0, m0)
+        sec = t0 / c0 * 1e-3
+        hbm_bound = by0 / (peaks["hbm_gbs"] * 1e9) > fl0 / (peaks["tflops_sustained"] * 1e12)
+        if n0 == "ffn_ln_h16":
+            label = "ffn_ln_tcgen05_kernel M=%d d=%d F=%d" % (m0["M"], m0["N"], m0["K"])
+        else:
+            label = "%s M=%d N=%d K=%d" % ("gemm_ln_tcgen05_kernel" if n0 == "gemm_ln_h16"
+                                           else "gemm_h16_tcgen05_kernel", m0["M"], m0["N"], m0["K"])
+        # DRAM and L2->SM bytes per launch of this kernel from the committed ncu capture of the kernel INSIDE a full
+        # step replay (tools/ncu_traffic.py regenerates profiles/traffic.json); None when no capture matches the label
+        traffic, l2_to_sm = None, None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            ent = json.load(open(tpath)).get(label, {})
+            traffic, l2_to_sm = ent.get("dram_bytes_per_launch"), ent.get("l2_to_sm_bytes_per_launch")
+        if hbm_bound:
+            ach, peak, unit = by0 / sec / 1e9, peaks["hbm_gbs"], "GB/s"
+        else:
+            ach, peak, unit = fl0 / sec / 1e12, peaks["tflops_sustained"], "TFLOP/s"
+        roof = {"bound": "hbm" if hbm_bound else "tensor", "kernel": label, "achieved": ach, "peak": peak,
+                "unit": unit, "frac": ach / peak, "traffic": traffic, "traffic_l2_to_sm": l2_to_sm,
+                "traffic_over_algorithmic": (traffic / by0) if traffic else None,
+                "l2_to_sm_over_algorithmic": (l2_to_sm / by0) if l2_to_sm else None,
+                "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
+                "launch_ms": t0 / c0, "share_of_step": t0 / tot, "algorithmic_bytes_per_launch": by0,
+                "algorithmic_flops_per_launch": fl0,
+                "tensor_tflops_same_kernel": fl0 / sec / 1e12,
+                "all_gemms": {"achieved": fl_all / (tt * 1e-3) / 1e12, "unit": "TFLOP/s",
+                              "frac_of_tensor_peak": fl_all / (tt * 1e-3) / 1e12 / peaks["tflops_sustained"],
+                              "share_of_step": tt / tot}}
+    if profile_out:
+        with open(profile_out, "w") as fh:
+            json.dump({"workload": workload_name(c.workload, c.cfg, c.B, c.T, D, c.use_cfg), "eager_denoise_steps": 6,
+                       "total_ms": tot, "kernels": [{"name": n, "meta": m, "launches": cnt, "total_ms": t,
+                                                     "share": t / tot} for n, m, cnt, t in breakdown]}, fh, indent=1)
+    return roof
