@@ -447,3 +447,143 @@ def dominant_kernel_roofline(c, peaks, profile_out):
                        "total_ms": tot, "kernels": [{"name": n, "meta": m, "launches": cnt, "total_ms": t,
                                                      "share": t / tot} for n, m, cnt, t in breakdown]}, fh, indent=1)
     return roof
+
+
+def run_b200(args):
+    from gesturediffusion_b200 import _cabi
+    from gesturediffusion_b200 import dist as gdist
+    from gesturediffusion_b200 import sampler as S
+
+    rank, world = gdist.init_process_group()
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch N>1 under torch.distributed.run)" % (args.gpus, world))
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    _cabi.load()                                     # fail loudly if the CUDA library is missing
+
+    cfg, sd, B, T = build_case(args.workload, args.batch, args.frames)
+    D = args.denoise_steps
+    use_cfg = not args.no_cfg
+    peaks = measured_peaks()
+    # model: rank 0's weights are the job's weights (broadcast of the packed arenas), seed broadcast
+    c = Case(args.workload, B, T, D, args.precision, use_cfg, rank, world, dev, rank * B, 20261104, cfg_sd=(cfg, sd))
+    c.global_batch = B * world
+    eng, dif = c.eng, c.dif
+
+    for _ in range(max(args.warmup, 3)):
+        c.one_call(False)
+    c.one_call(True)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = _cabi.launch_count() + S.STATS["graph_kernels"]
+    ms_total = c.timed(args.steps, False)
+    launches = _cabi.launch_count() + S.STATS["graph_kernels"] - l0
+    ms_e2e = c.timed(args.steps, True)
+    clocks = sampler.stop() if sampler else None
+
+    frames = B * world * T * args.steps
+    value = frames / (ms_total * 1e-3)
+    ms_step = ms_total / args.steps
+    e2e_value = frames / (ms_e2e * 1e-3)
+    gather_ms = c.timed_gather()
+
+    extra = {}
+    if not args.skip_extras:
+        dif1000 = c.make_dif("")
+        c.one_call(False, dif1000, skip=990)                   # builds this schedule's step graph (10 steps)
+        ms1000 = c.timed(1, False, dif1000)
+        extra["ddpm1000"] = {"value": B * world * T / (ms1000 * 1e-3), "unit": "frames/s",
+                             "ms_per_denoise_step": ms1000 / 1000.0, "calls": 1}
+
+        # SURVEY 8.6 rows on the same workload, rank-local (no gather): 50-step DDIM (eta 0) and, for the 6-interleaved
+        # GENEA layout, a 4-chunk take through generate_take (seed hand-off + de-normalise/split on the device)
+        def timed_local(fn):
+            fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1)
+        dif_ddim = c.make_dif("ddim%d" % D)
+        ms_ddim = timed_local(lambda: dif_ddim.ddim_sample_loop(c.model, c.shape, clip_denoised=False,
+                                                                model_kwargs={"y": c.y_dev}, eta=0.0))
+        extra["ddim%d" % D] = {"value": B * T / (ms_ddim * 1e-3), "unit": "frames/s per GPU",
+                               "ms_per_denoise_step": ms_ddim / D}
+        if c.J % 6 == 0 and use_cfg:
+            from gesturediffusion_b200.generate import generate_take
+            chunks = [c.y_dev] * 4
+            mean, std = torch.zeros(c.J, device=dev), torch.ones(c.J, device=dev)
+            ms_take = timed_local(lambda: generate_take(c.model, dif, chunks, B, T, seed_poses=cfg["seed_poses"],
+                                                        guidance_param=GUIDANCE, mean=mean, std=std))
+            extra["take4"] = {"value": 4 * B * T / (ms_take * 1e-3), "unit": "frames/s per GPU", "chunks": 4,
+                              "ms_per_denoise_step": ms_take / (4 * D)}
+
+    # ---- roofline of the dominant kernel: CUDA events around every launch of an eager denoise pass (rank 0)
+    roof = dominant_kernel_roofline(c, peaks, args.profile_out) if rank == 0 else None
+    flops_step = eng.flops_per_step(B, T, 2 if use_cfg else 1)
+    weights_mb = sum(a.numel() * a.element_size() for a in eng.arenas.values()) // 2 ** 20
+    broadcast_ms, h2d, d2h = c.broadcast_ms, c.h2d, c.d2h
+
+    if not args.skip_extras and args.workload == "cfg2a":
+        c.free()
+        # configs[3]: KIT shape, GLOBAL batch 1024 sharded over the ranks (strong scaling; N = 1 holds all 1024)
+        lo, hi = gdist.shard_range(CFG4_GLOBAL_BATCH, rank, world)
+        extra["cfg4"] = extra_case("cfg4", hi - lo, 196, D, args, rank, world, dev, lo, CFG4_GLOBAL_BATCH, 2, peaks)
+        extra["cfg4"]["scaling"] = "strong (global batch %d / %d ranks)" % (CFG4_GLOBAL_BATCH, world)
+        # configs[2]: the reference's native gesture config, batch 128 per GPU (weak)
+        extra["cfg3"] = extra_case("cfg3", 128, 120, D, args, rank, world, dev, rank * 128, 128 * world, 3, peaks)
+        # configs[1] as quoted: V2 + text conditioning, T = 200, CFG, the full 1000-step schedule
+        extra["cfg2b"] = extra_case("cfg2b", 64, 200, D, args, rank, world, dev, rank * 64, 64 * world, 1, peaks,
+                                    respacing="")
+
+    if rank != 0:
+        return
+    step_tflops = flops_step / (ms_step / D * 1e-3) / 1e12
+    line = {"metric": "motion frames/sec (CFG DDPM sampling)", "value": value, "unit": "frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "ms_per_denoise_step": ms_step / D, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp16": "f16 operands / f32 accumulate", "bf16": "bf16 operands / f32 accumulate",
+                      "fp32": "f32"}[args.precision],
+            "precision_note": PRECISION_NOTE if args.precision == "fp16" else None,
+            "data": "synthetic (random-init weights of the reference architecture, N(0,1) seed poses / MFCC)",
+            "config": {"workload": workload_name(args.workload, cfg, B, T, D, use_cfg), "global_batch": B * world,
+                       "frames": T, "denoise_steps": D, "guidance": GUIDANCE if use_cfg else None,
+                       "parallelism": "dp%d (batch-sharded, no per-step collective)" % world,
+                       "noise": "in-kernel Philox4x32-10 keyed by (seed, global sample, step)",
+                       "l2": "per-denoise-step working set ~%d MB of activations > 126 MB L2; weights (%d MB) stay "
+                             "L2-resident as in production" % (2 * B * (T + 1) * 12 * cfg["latent_dim"] * 2 // 2 ** 20,
+                                                               weights_mb),
+                       "e2e_path": "H2D of y from pinned memory, p_sample_loop, every rank copies its own shard of the "
+                                   "motions D2H to pinned memory (no device gather on the e2e path); value path: "
+                                   "device-resident y, all-gather of the motions"},
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d * world,
+                    "d2h_bytes_per_step": d2h * world, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches), "broadcast_ms": broadcast_ms, "gather_ms": gather_ms,
+            "step_roofline": {"bound": "tensor", "achieved": step_tflops, "peak": peaks["tflops_sustained"],
+                              "unit": "TFLOP/s", "frac": step_tflops / peaks["tflops_sustained"],
+                              "algorithmic_gflop_per_denoise_step": flops_step / 1e9},
+            "roofline": roof, "clocks": clocks}
+    line.update(extra)
+    if world == 1 and not args.skip_cpu_baseline:
+        threads = os.cpu_count() or 1
+        sb, ss = cpu_sample_plan(B, D)
+        fps, ms_c, kind, desc = cpu_rate(cfg, sd, T, D, use_cfg, sb, ss, threads)
+        line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind, "sample": desc,
+                                "ms_per_denoise_step_at_sample_batch": ms_c, "same_batch": sb == B}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+        import torch.distributed as _dist
+        if _dist.is_available() and _dist.is_initialized():
+            _dist.destroy_process_group()
