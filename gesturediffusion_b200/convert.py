@@ -32,6 +32,8 @@ def _convert_model(ref, device, precision):
     if inner is not None:
         return ClassifierFreeSampleModel(_convert_model(inner, device, precision))
     name = type(ref).__name__
+    if name not in ("MDM", "MDM_Old"):
+        raise TypeError("cannot accelerate a %s" % name)
     common = dict(njoints=ref.njoints, nfeats=ref.nfeats, pose_rep=ref.pose_rep, data_rep=ref.data_rep,
                   latent_dim=ref.latent_dim, ff_size=ref.ff_size, num_layers=ref.num_layers,
                   num_heads=ref.num_heads, dropout=0.1, activation=ref.activation, dataset=ref.dataset,

@@ -16,6 +16,19 @@ CHAIN_CASES = ["chain_v1_small_cfg5", "chain_v2_small_cfg5", "chain_v1_small_unc
                "chain_v2_gesture_cfg50"]
 
 
+def record_parity(line):
+    """Print a measured parity error and append it to the artefact the round keeps (profiles/r02_parity.txt is a copy
+    of gpurun_out/parity.txt from the GPU box; GD_PARITY_LOG overrides the path, empty string turns it off)."""
+    print(line)
+    path = os.environ.get("GD_PARITY_LOG")
+    if path is None:
+        out = os.path.join(os.path.dirname(os.path.dirname(GOLDEN)), "gpurun_out")
+        path = os.path.join(out, "parity.txt") if os.path.isdir(out) else ""
+    if path:
+        with open(path, "a") as fh:
+            fh.write(line + "\n")
+
+
 def rel_l2(a, b):
     a, b = a.double().cpu().reshape(-1), b.double().cpu().reshape(-1)
     return float((a - b).norm() / b.norm())
