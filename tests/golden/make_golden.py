@@ -42,6 +42,9 @@ CHAIN_CASES = {
     "chain_v1_small_inpaint": ("v1_small", [4], True, dict(inpaint=True)),
     "chain_v1_humanml_uncond50": ("v1_humanml", [50], False, {}),  # BASELINE config 1 in full
     "chain_v2_gesture_cfg50": ("v2_gesture", [50], True, {}),      # BASELINE config 3 at B=2
+    # the reference's DEFAULT schedule: all 1000 steps (utils/model_util.py:42,49-50), CFG -- BASELINE config 2's schedule
+    "chain_v1_small_cfg1000": ("v1_small", [1000], True, {}),
+    "chain_v2_small_cfg1000": ("v2_small", [1000], True, {}),
 }
 
 
@@ -98,9 +101,11 @@ def model_fixtures():
         print("model_%s.npz" % case, tuple(cond.shape))
 
 
-def chain_fixtures():
+def chain_fixtures(only=None):
     ns = ref_shims.load_reference()
     for name, (case, resp, use_cfg, extra) in CHAIN_CASES.items():
+        if only and name not in only:
+            continue
         cfg, sd, m, x, y = build(case)
         dif = ref_shims.build_reference_diffusion(resp)
         model = ns.ClassifierFreeSampleModel(m) if use_cfg else m
@@ -198,6 +203,9 @@ def take_fixtures():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
+    if len(sys.argv) > 1:                       # python make_golden.py chain_x chain_y: only these chain fixtures
+        chain_fixtures(only=set(sys.argv[1:]))
+        sys.exit(0)
     schedule_fixture()
     model_fixtures()
     chain_fixtures()

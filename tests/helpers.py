@@ -13,7 +13,7 @@ MODEL_CASES = ["v1_small", "v2_small", "v2_small_text", "v1_humanml", "v1_kit", 
 SMALL_MODEL_CASES = ["v1_small", "v2_small", "v2_small_text"]
 CHAIN_CASES = ["chain_v1_small_cfg5", "chain_v2_small_cfg5", "chain_v1_small_uncond4_skip",
                "chain_v2_small_const_noise", "chain_v1_small_inpaint", "chain_v1_humanml_uncond50",
-               "chain_v2_gesture_cfg50"]
+               "chain_v2_gesture_cfg50", "chain_v1_small_cfg1000", "chain_v2_small_cfg1000"]
 
 
 def record_parity(line):

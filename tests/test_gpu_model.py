@@ -1,13 +1,18 @@
 """GPU: the drop-in API end to end (MDM / MDM_Old / ClassifierFreeSampleModel / SpacedDiffusion), through
 the C ABI, against (a) golden outputs of the unmodified reference and (b) the CPU oracle on fresh inputs.
 
-Tolerances are the north star's: per-step model / x0 prediction 1e-5 relative L2 in fp32 mode and 2e-3 in
-16-bit mode; final motion of a 50-step chain 1e-2.  Noise is injected identically on both sides."""
+Tolerances: the north star's 1e-5 per-step relative L2 in fp32 mode and 2e-3 in the 16-bit mode, 1e-2 for the final
+motion of a chain.  The 16-bit mode held to 2e-3 is fp16 (the package default, what bench.py times); bf16 operands (the
+same kernels) are bounded by bf16's own rounding at 3-4.5e-3 per forward (tools/sim_16bit_rounding.py) and are a stated
+deviation (bench.py `precision_note`), tested here only against that looser bound.  Two fp32 entries are
+looser than 1e-5 because they bound accumulated, not per-step, error: the guided combination u + 2.5 (c - u) and a whole
+chain.  Every measured error is appended to gpurun_out/parity.txt (helpers.record_parity; kept as profiles/r02_parity.txt).
+Noise is injected identically on both sides."""
 import pytest
 import torch
 
-from helpers import (CHAIN_CASES, MODEL_CASES, build_product_model, load_chain_case, load_model_case, rel_l2,
-                     to_dev)
+from helpers import (CHAIN_CASES, MODEL_CASES, build_product_model, load_chain_case, load_model_case, record_parity,
+                     rel_l2, to_dev)
 
 pytestmark = pytest.mark.gpu
 
@@ -40,7 +45,7 @@ def test_forward_matches_reference_golden(cuda_device, case, precision):
     unc = m(xd, t, yu)
     guided = ClassifierFreeSampleModel(m)(xd, t, yd)
     errs = (rel_l2(cond, gold["cond"]), rel_l2(unc, gold["uncond"]), rel_l2(guided, gold["guided"]))
-    print("forward %s %s: cond %.2e uncond %.2e guided %.2e" % ((case, precision) + errs))
+    record_parity("forward %s %s: cond %.2e uncond %.2e guided %.2e" % ((case, precision) + errs))
     assert errs[0] < TOL[precision] and errs[1] < TOL[precision]
     assert errs[2] < GUIDED_TOL[precision]
 
@@ -60,7 +65,7 @@ def test_forward_matches_oracle_fresh_inputs(cuda_device, arch, precision):
         m = build_product_model(cfg, sd, cuda_device, precision)
         out = m(x.to(cuda_device), t.to(cuda_device), to_dev(y, cuda_device))
         err = rel_l2(out, ref)
-        print("fresh %s %s B=%d T=%d: %.2e" % (arch, precision, B, T, err))
+        record_parity("fresh %s %s B=%d T=%d: %.2e" % (arch, precision, B, T, err))
         assert err < TOL[precision]
 
 
@@ -84,7 +89,7 @@ def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
     finally:
         eng.fuse_ffn_min_rows = min_rows
     err = rel_l2(fused, gold["cond"])
-    print("fused ffn %s %s: %.2e (vs two-kernel path %.2e)" % (case, precision, err, rel_l2(fused, base)))
+    record_parity("fused ffn %s %s: %.2e (vs two-kernel path %.2e)" % (case, precision, err, rel_l2(fused, base)))
     assert err < TOL[precision]
     assert rel_l2(fused, base) < TOL[precision]
 
@@ -140,7 +145,7 @@ def test_chain_matches_reference_golden(cuda_device, case, precision):
     assert len(outs) == meta["n_exec"]
     first_pred = rel_l2(outs[0]["pred_xstart"], gold["trace_pred"][0])
     final = rel_l2(outs[-1]["sample"], gold["final"])
-    print("chain %s %s: first pred_xstart %.2e final %.2e" % (case, precision, first_pred, final))
+    record_parity("chain %s %s: first pred_xstart %.2e final %.2e" % (case, precision, first_pred, final))
     assert first_pred < GUIDED_TOL[precision] if meta["cfg"] else first_pred < TOL[precision]
     assert final < CHAIN_TOL[precision]
     for j, i in enumerate(gold["trace_idx"]):
@@ -270,5 +275,5 @@ def test_full_size_properties(cuda_device, arch, J, T, B):
                 parts.append(dif.p_sample_loop(model, sh, clip_denoised=False, model_kwargs=kwr))
             assert torch.equal(torch.cat(parts, dim=0), outs["fp16"])
     err = rel_l2(outs["fp16"], outs["fp32"])
-    print("full size %s: fp16 vs fp32 mode after 50 steps %.2e" % (arch, err))
+    record_parity("full size %s: fp16 vs fp32 mode after 50 steps %.2e" % (arch, err))
     assert err < CHAIN_TOL["fp16"]

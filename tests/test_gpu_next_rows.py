@@ -3,7 +3,7 @@ outputs (tests/golden), through the C ABI; tolerances as in test_gpu_model.py.""
 import pytest
 import torch
 
-from helpers import (DDIM_CASES, TAKE_CASES, build_product_model, load_ddim_case, load_take_case, rel_l2, to_dev)
+from helpers import (DDIM_CASES, TAKE_CASES, build_product_model, load_ddim_case, load_take_case, record_parity, rel_l2, to_dev)
 
 pytestmark = pytest.mark.gpu
 
@@ -29,7 +29,7 @@ def test_ddim_matches_reference_golden(cuda_device, case, precision):
     outs = list(dif.ddim_sample_loop_progressive(model, tuple(x.shape), **args))
     assert len(outs) == meta["n_exec"]
     errs = [rel_l2(o["sample"], gold["trace_sample"][i]) for i, o in enumerate(outs)]
-    print("ddim %s %s: per-step sample err max %.2e, final %.2e" % (case, precision, max(errs), errs[-1]))
+    record_parity("ddim %s %s: per-step sample err max %.2e, final %.2e" % (case, precision, max(errs), errs[-1]))
     assert max(errs) < CHAIN_TOL[precision]
     assert rel_l2(outs[-1]["pred_xstart"], gold["trace_pred"][-1]) < CHAIN_TOL[precision]
     final = dif.ddim_sample_loop(model, tuple(x.shape), **args)
@@ -75,7 +75,7 @@ def test_take_matches_reference_golden(cuda_device, case, precision):
     for k in ("sample", "motion", "motion_rot"):
         assert out[k].is_cuda and tuple(out[k].shape) == tuple(gold[k].shape)
         err = rel_l2(out[k], gold[k])
-        print("take %s %s %s: %.2e" % (case, precision, k, err))
+        record_parity("take %s %s %s: %.2e" % (case, precision, k, err))
         assert err < CHAIN_TOL[precision]
 
 
