@@ -211,6 +211,21 @@ def layernorm(x, gamma, beta, out_f32=None, out_h16=None, eps=1e-5, rows=None):
     _cabi.check(rc, "gd_layernorm")
 
 
+def linear_res_ln_f32_noalloc(a, w, bias, residual, gamma, beta, out_f32=None, out_h16=None, eps=1e-5):
+    """LayerNorm(residual + a @ w^T + bias) * gamma + beta on the fp32 path with the [M, N] intermediate in the
+    library's built-in static scratch (gd_linear_res_ln_f32_noalloc: no workspace argument, no allocation; M * N is
+    limited to gd_noalloc_max_elems(); calls on one device share the scratch and must not overlap on the GPU)."""
+    lib = _cabi.load()
+    M, N, K = a.shape[0], w.shape[0], a.shape[1]
+    rc = lib.gd_linear_res_ln_f32_noalloc(_dev(a, torch.float32, "A"), a.stride(0), _dev(w, torch.float32, "W"),
+                                          w.stride(0), M, N, K, _dev(bias, torch.float32, "bias"),
+                                          _dev(residual, torch.float32, "residual"), residual.stride(0),
+                                          _dev(gamma, torch.float32, "gamma"), _dev(beta, torch.float32, "beta"), eps,
+                                          _dev(out_f32, torch.float32, "out_f32"), _dev(out_h16, "h16", "out_h16"),
+                                          fmt_of(out_h16), _cabi.stream_handle())
+    _cabi.check(rc, "gd_linear_res_ln_f32_noalloc")
+
+
 def local_attention(z, rope_cos, rope_sin, x_f32, x_h16, n_seq, T, d, heads, window=10):
     lib = _cabi.load()
     with _Timed("local_attention", n_seq=n_seq, T=T, d=d):

@@ -12,7 +12,7 @@
  *    back inside a call, so every call is CUDA-graph capturable;
  *  - return 0 on success, negative gdStatus otherwise; gd_last_error() gives the message
  *    (thread-local, host pointer);
- *  - row-major everywhere; "act" buffers are bf16 in bf16 mode and fp32 in fp32 mode;
+ *  - row-major everywhere; "act" buffers are fp16 (default) or bf16 in the 16-bit modes and fp32 in fp32 mode;
  *  - weights use the nn.Linear layout W[N][K] (K contiguous) exactly as in the reference
  *    state_dict, so y = x @ W^T + b.
  */
@@ -142,6 +142,22 @@ int gd_attention_f32(const float* qkv, float* out, int32_t n_seq, int32_t S, int
  * fp32 and/or 16-bit (`h16_fmt`) out (either may be NULL). */
 int gd_layernorm(const float* in, const float* gamma, const float* beta, float* out_f32,
                  void* out_h16, int32_t h16_fmt, int32_t rows, int32_t d, float eps, void* stream);
+
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The fp32-mode post-norm
+ * sub-layer tail  X = LayerNorm(residual + A[M,K] @ W[N,K]^T + bias) * gamma + beta  = gd_gemm_f32 (residual
+ * epilogue) -> [M, N] fp32 scratch -> gd_layernorm, with the scratch in a file-scope `static __device__` array inside
+ * the library instead of a caller workspace; the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limit: M * N <= gd_noalloc_max_elems() = 1 Mi fp32 elements (4 MiB, held by every GPU that loads the library until
+ * exit); larger problems return GD_ERR_INVALID with a message.  N as gd_layernorm (multiple of 128 in [128, 1024]).
+ * All calls on a device SHARE the array, which keeps the previous call's contents (nothing needs to start at zero:
+ * the GEMM overwrites the whole [M, N] region before it is read); calls that overlap on the GPU -- different streams,
+ * concurrent graph replays -- race on it.  The device must be current when the call is made. */
+int gd_noalloc_max_elems(void);
+int gd_linear_res_ln_f32_noalloc(const float* A, int32_t lda, const float* W, int32_t ldw, int32_t M, int32_t N,
+                                 int32_t K, const float* bias, const float* residual, int32_t ld_res,
+                                 const float* gamma, const float* beta, float eps, float* out_f32, void* out_h16,
+                                 int32_t h16_fmt, void* stream);
 
 /* RoPE + causal windowed LocalAttention + second RoPE (mdm.py:176-213; local_attention.py:43-62,
  * 92-172): z [n_seq, T, d] fp32 -> encoder-input rows 1..T of each sequence (token 0 is written by
