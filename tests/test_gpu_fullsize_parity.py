@@ -79,7 +79,7 @@ def test_guided_loop_with_unaligned_uncond_half(cuda_device, arch, J, T, B, prec
     assert torch.equal(outs[0], outs[1])
     err = rel_l2(outs[0], ref)
     record_parity("unaligned uncond %s J=%d T=%d B=%d %s: final %.2e" % (arch, J, T, B, precision, err))
-    assert err < (1e-2 if precision == "fp16" else 2e-4)
+    assert err < (1e-2 if precision == "fp16" else 1e-5)
     # the non-uniform-t eager path slices model_out per sample (gaussian_diffusion.py _posterior): same fault class
     t = torch.arange(B, dtype=torch.long) + 1
     dif = create_gaussian_diffusion(timestep_respacing=[4])

@@ -8,7 +8,7 @@ from helpers import (DDIM_CASES, TAKE_CASES, build_product_model, load_ddim_case
 pytestmark = pytest.mark.gpu
 
 PRECISIONS = ["fp32", "fp16", "bf16"]
-CHAIN_TOL = {"fp32": 2e-4, "fp16": 1e-2, "bf16": 1e-2}
+CHAIN_TOL = {"fp32": 1e-5, "fp16": 1e-2, "bf16": 1e-2}
 
 
 def _diffusion(resp):
