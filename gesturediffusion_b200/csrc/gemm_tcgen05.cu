@@ -413,6 +413,22 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
                          pack_h16x2(w[2], w[3], ep.h16_fmt), pack_h16x2(w[4], w[5], ep.h16_fmt),
                          pack_h16x2(w[6], w[7], ep.h16_fmt));
           }
+          if (dbg & 32) {
+            // experiment (GD_GEMM_DBG=32, results right): leave through coalesced generic-proxy stores instead of the
+            // TMA -- 8 lanes read one staged 128-byte row segment back and write it as one full line, 4 rows per
+            // instruction -- so that the stores do not queue behind the producer's operand loads in the TMA unit
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int rl = i * 4 + (lane >> 3), c8 = lane & 7;
+              const uint4 q = ptx::lds_v4u(stg + rl * 128 + ((c8 ^ (rl & 7)) << 4));
+              const int mm = m_warp + rl, n = n0 + c8 * 8;
+              if (mm < M && n < N)
+                *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(ep.out_h16) + (size_t)mm * ep.ld_out_h16 + n) = q;
+            }
+            __syncwarp();
+            continue;
+          }
           ptx::fence_proxy_async();                          // generic-proxy smem writes -> visible to the TMA
           __syncwarp();
           if (lane == 0 && !(dbg & 16)) {

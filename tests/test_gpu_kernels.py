@@ -53,9 +53,10 @@ def test_gemm_bias(cuda_device, M, N, K, dtype):
 @pytest.mark.parametrize("M,N,K", [(700, 1024, 512), (129, 512, 64), (25216, 1024, 512)])
 @pytest.mark.parametrize("dtype", ["bf16", "fp16"])
 def test_gemm_specialised_epilogues(cuda_device, M, N, K, dtype):
-    """The three compile-time epilogues of the tcgen05 GEMM (bias->16 bit, bias+erf-GELU->16 bit with the
-    polynomial erfc form, bias+residual->fp32) against float64; the GELU path must agree with the exact erf
-    form to within one 16-bit rounding of the output, i.e. its own error (6e-7 abs) is invisible."""
+    """The three compile-time epilogues of the tcgen05 GEMM (bias->16 bit, bias+erf-GELU->16 bit in the tanh-of-fitted-
+    polynomial form of common.cuh::gelu_fast, bias+residual->fp32) against float64.  The GELU path is held to its stated
+    accuracy: per element one 16-bit ulp of the result + the fit's 2.5e-5 + the MUFU.TANH bound 0.5 |x| 2^-11, and in
+    relative L2 about one extra output rounding."""
     Kn = _K()
     tdt = TDT[dtype]
     g = torch.Generator(device="cuda").manual_seed(M + K)
@@ -69,13 +70,14 @@ def test_gemm_specialised_epilogues(cuda_device, M, N, K, dtype):
     assert rel_l2(oh.float(), base) < H16_ROUND[dtype]
     Kn.gemm(a, w, Kn.epilogue(bias=bias, act=Kn.GD_ACT_GELU_ERF, out_h16=oh))
     ref = _gelu(base)
-    assert rel_l2(oh.float(), ref) < H16_ROUND[dtype]
-    # versus the correctly rounded exact value: never more than one 16-bit ulp away, and almost always equal
+    e_gelu = rel_l2(oh.float(), ref)
+    record_parity("gelu epilogue %s M=%d N=%d K=%d: rel-L2 vs float64 erf-GELU %.2e" % (dtype, M, N, K, e_gelu))
+    assert e_gelu < 1.5 * H16_ROUND[dtype]
     exact = ref.to(torch.float32).to(tdt)
     ulp = exact.float().abs() * (2.0 ** -10 if dtype == "fp16" else 2.0 ** -7)
     diff = (oh.float() - exact.float()).abs()
-    assert bool((diff <= 1.01 * ulp + 3e-6).all())        # 3e-6: fp32 accumulation order + the 6e-7 erfc fit
-    assert float((diff > 0).float().mean()) < 0.05      # rounding flips from the fp32 accumulation order (measured 2 %)
+    bound = 1.01 * ulp + 3e-5 + 0.5 * base.abs().float() * 2.0 ** -11
+    assert bool((diff <= bound).all()), float((diff - bound).max())
     o32 = torch.empty(M, N, device="cuda")
     Kn.gemm(a, w, Kn.epilogue(bias=bias, residual=res, out_f32=o32))
     assert rel_l2(o32, base + res.double()) < 1e-5
@@ -346,10 +348,15 @@ def test_ffn_ln_split(cuda_device, M, F, dtype):
     out_lo = torch.full_like(lo, 3.0)
     Kn.ffn_ln_split(hi, lo, w1, b1, w2, b2, gamma, beta, out_hi=out_hi, out_lo=out_lo)
     got = out_hi.float() + out_lo.float()
-    tol = 3e-5 if dtype == "fp16" else 3e-4
-    assert rel_l2(got, ref) < tol
+    # vs float64: the (hi, lo) output rounding + the GELU form's own error (gelu_fast: fit 2.5e-5 + MUFU.TANH 2^-11, about
+    # 2e-4 relative on H, 5e-5 here); vs the two-kernel path (same GELU, same roundings): accumulation order only
+    tol = 1e-4 if dtype == "fp16" else 3e-4
+    tol_same = 3e-5 if dtype == "fp16" else 3e-4
+    e64, e2k = rel_l2(got, ref), rel_l2(got, hi_ref.float() + lo_ref.float())
+    record_parity("ffn_ln_split %s M=%d F=%d: vs float64 %.2e, vs two-kernel path %.2e" % (dtype, M, F, e64, e2k))
+    assert e64 < tol
     assert rel_l2(hi_ref.float() + lo_ref.float(), ref) < tol
-    assert rel_l2(got, hi_ref.float() + lo_ref.float()) < tol
+    assert e2k < tol_same
     # in place, hi only (last sub-layer)
     hi2, lo2 = hi.clone(), lo.clone()
     Kn.ffn_ln_split(hi2, lo2, w1, b1, w2, b2, gamma, beta, out_hi=hi2)
