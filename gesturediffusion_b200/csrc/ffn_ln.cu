@@ -33,6 +33,12 @@
 // (gd_ffn_trace, tools/trace_ffn.py) shows the limits: TMEM (Y 256 columns + two 128-column chunk accumulators = all
 // 512 columns) forces N = 128 for GEMM1 (three quarters of the N = 256 rate), four 32 KB operand stages deliver
 // ~57 B/clk, and the GELU chunks + LayerNorm tail keep the eight epilogue warps busy ~20 k of a tile's ~38 k clocks.
+// Round 2 measurements (profiles/r02c_ffn_dbg_knobs.txt, r02f_trace_ffn_stg_passB.txt): without ANY operand loads the
+// kernel still takes 64 of 71 us and without loads, GELU arithmetic, stores and H exchange 56 us, so the tile is paced
+// by its dependency chain (GEMM1 -> GELU -> exchange -> GEMM2 -> LayerNorm tail on ONE set of epilogue warps with a
+// single-buffered output accumulator), not by the feed.  The GELU arithmetic is issue-bound: the 9-instruction
+// gelu_fast took the kernel from 71 to 66 us.  Replacing pass B's TMA stores by coalesced generic stores was slower
+// (pass B 8.2 k vs 7.7 k clocks, kernel 71 vs 66 us) and was dropped.
 #include <stdlib.h>
 
 #include "common.cuh"
