@@ -14,7 +14,7 @@ GD_ACT_NONE, GD_ACT_GELU_ERF, GD_ACT_SILU = 0, 1, 2
 GD_F32, GD_BF16, GD_FP16 = 0, 1, 2
 
 EXPORTED_SYMBOLS = [
-    "gd_abi_version", "gd_last_error", "gd_gemm_h16", "gd_gemm_f32", "gd_gemm_h16_ln", "gd_gemm_h16_ln_split", "gd_ffn_h16_ln_split", "gd_ffn_trace", "gd_set_l2_window", "gd_attention_h16",
+    "gd_abi_version", "gd_last_error", "gd_gemm_h16", "gd_gemm_f32", "gd_gemm_h16_ln", "gd_gemm_h16_ln_split", "gd_ffn_h16_ln_split", "gd_ffn_trace", "gd_attention_h16",
     "gd_attention_f32", "gd_layernorm", "gd_local_attention", "gd_cond_tokens", "gd_posterior_step",
     "gd_pack_rows", "gd_unnormalize_split", "gd_q_sample", "gd_philox_normal", "gd_set_loop_state", "gd_launch_count",
     "gd_noalloc_max_elems", "gd_linear_res_ln_f32_noalloc",
@@ -84,7 +84,6 @@ def load():
         "gd_ffn_h16_ln_split": [_p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _i32, _i32, _i32, _i32, _p, _p, _f32, _p, _p,
                                 _i32, _p],
         "gd_ffn_trace": [_p],
-        "gd_set_l2_window": [_p, _i64, _p],
         "gd_attention_h16": [_p, _p, _i32, _i32, _i32, _i32, _i32, _p],
         "gd_attention_f32": [_p, _p, _i32, _i32, _i32, _i32, _p],
         "gd_layernorm": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _f32, _p],

@@ -16,8 +16,6 @@ namespace gd {
 void set_error(const char* fmt, ...);
 extern std::atomic<long long> g_launches;
 extern unsigned long long* g_ffn_trace;     // debug timeline buffer (gd_ffn_trace), NULL = off
-// L2 persisting access-policy window attached to every launch_pdl launch (gd_set_l2_window); num_bytes 0 = off
-extern cudaAccessPolicyWindow g_l2_window;
 
 #define GD_REQUIRE(cond, ...)                                 \
   do {                                                        \
@@ -58,16 +56,11 @@ inline cudaError_t launch_pdl(int kind, void (*kernel)(KArgs...), dim3 grid, dim
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[1];
   int n = 0;
   if (pdl_enabled(kind)) {
     attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[n].val.programmaticStreamSerializationAllowed = 1;
-    ++n;
-  }
-  if (g_l2_window.num_bytes != 0) {                          // keep the residual stream resident in L2 (gd_set_l2_window)
-    attr[n].id = cudaLaunchAttributeAccessPolicyWindow;
-    attr[n].val.accessPolicyWindow = g_l2_window;
     ++n;
   }
   cfg.attrs = attr;

@@ -59,7 +59,6 @@ struct LnParams {
   float eps;
   int M, K;
   uint32_t idesc;
-  unsigned long long* trace;   // gd_ffn_trace timeline buffer (gemm_lnr_tcgen05_kernel only), NULL = off
   int dbg;     // GD_LN_DBG diagnostics (results wrong): 1 no statistics exchange, 2 no global stores, 4 no residual, 8 no epilogue
 };
 
@@ -455,378 +454,6 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   }
 }
 
-// ---------------------------------------------------------------------------------------------------------------
-// gemm_lnr_tcgen05_kernel: the split-residual form (pair in, pair out, N = 512) with the RESIDUAL ADDED ON THE TENSOR
-// PIPE.  After the tile's K loop the MMA warp issues  Y[:, 64 s ..] += X_hi[:, 64 s ..] I^T + X_lo[:, 64 s ..] I^T
-// (s = 0..3, I = 64 x 64 identity as the K-major B operand; products with 1.0 and fp32 accumulation: the same sum the
-// explicit add makes).  The operands travel through the ordinary stage ring: a residual stage is
-// [X_hi 128x64 | X_lo 128x64 | I 8 KB] -- the identity is a pre-swizzled 8 KB constant fetched with a plain bulk
-// copy into the unused part of the stage, so no shared memory is added.  What that buys in the epilogue (which paces
-// this kernel: 8 K blocks of MMAs per tile against two passes over the accumulator):
-//   * pass A only READS the accumulator (y = acc + bias, running (mean, M2)): no per-warp residual ring, no waits
-//     for residual boxes (two in flight per warp exposed 2 x the TMA latency per tile), no TMEM write-back;
-//   * both 4 KB blocks of a warp stage outputs, alternating, so a chunk never waits for the previous chunk's store.
-struct alignas(16) IdentityTable { uint16_t v[2][64 * 64]; };       // [fp16 | bf16]: I64 as 64 rows x 128 B, 128B-swizzled
-constexpr IdentityTable make_identity_table() {
-  IdentityTable t{};
-  for (int f = 0; f < 2; ++f)
-    for (int n = 0; n < 64; ++n)
-      for (int c = 0; c < 8; ++c)                            // 16-byte chunk c (k = 8c .. 8c+7) at position c ^ (n & 7)
-        for (int e = 0; e < 8; ++e)
-          t.v[f][n * 64 + ((c ^ (n & 7)) * 8) + e] = (8 * c + e == n) ? (f == 0 ? 0x3C00 : 0x3F80) : 0;
-  return t;
-}
-__device__ const IdentityTable g_identity64 = make_identity_table();   // constant-initialised: no run-time set-up
-
-template <int STAGES>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
-gemm_lnr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                        const __grid_constant__ CUtensorMap tmap_xhi, const __grid_constant__ CUtensorMap tmap_xlo,
-                        const __grid_constant__ CUtensorMap tmap_ohi, const __grid_constant__ CUtensorMap tmap_olo,
-                        const LnParams p, uint32_t idesc_res) {
-  constexpr int BN = 256;
-  using Cfg = LnCfg<BN, STAGES, true>;
-  constexpr int kLnStages = STAGES;
-  constexpr int N = 2 * BN;
-  extern __shared__ __align__(1024) uint8_t smem[];
-  if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
-  uint8_t* ring = smem + kLnStages * Cfg::kStageBytes;       // per epilogue warp two 4 KB staging blocks
-  float* vecs = reinterpret_cast<float*>(ring + Cfg::kRingBytes);                // bias | gamma | beta
-  uint8_t* stats = reinterpret_cast<uint8_t*>(vecs) + Cfg::kVecBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stats + Cfg::kStatBytes);
-  uint64_t* full_bar = bars;
-  uint64_t* empty_bar = full_bar + kLnStages;
-  uint64_t* tfull_bar = empty_bar + kLnStages;
-  uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* stat_bar = tempty_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
-
-  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform
-  const uint32_t rank = ptx::cluster_ctarank();
-  const int n_clusters = (int)gridDim.x >> 1, cluster_id = (int)blockIdx.x >> 1;
-  const int M = p.M;
-  const int m_tiles = (M + kLnBM - 1) / kLnBM;
-  const int k_blocks = (p.K + kLnBK - 1) / kLnBK;
-  const int n_cta = (int)rank * BN;
-  constexpr int kResStages = BN / kLnBK;                     // 4 residual stages per tile
-  // timeline of CTA 0 (tools/trace_ffn.py --kernel lnr): role 0 = epilogue warp 2 lane 0, role 1 = MMA warp, role 2 = producer
-  int tr_n = 0;
-  unsigned long long* tr_buf = nullptr;
-  if (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && warp <= 2)
-    tr_buf = p.trace + (warp == 2 ? 0 : (warp == 1 ? 4096 : 8192));
-  auto TR = [&](unsigned tag) {
-    if (tr_buf != nullptr && tr_n < 4096) tr_buf[tr_n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull);
-  };
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tensormap(&tmap_a);
-    ptx::prefetch_tensormap(&tmap_w);
-    ptx::prefetch_tensormap(&tmap_xhi);
-    ptx::prefetch_tensormap(&tmap_xlo);
-    ptx::prefetch_tensormap(&tmap_ohi);
-    ptx::prefetch_tensormap(&tmap_olo);
-  }
-  if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kLnStages; ++s) {
-      ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
-    }
-    for (int b = 0; b < 2; ++b) {
-      ptx::mbar_init(&tfull_bar[b], 1);
-      ptx::mbar_init(&tempty_bar[b], kLnEpiWarps);
-      ptx::mbar_init(&stat_bar[b], 1);
-    }
-    ptx::fence_barrier_init();
-  }
-  if (warp == 2) ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
-  for (int i = threadIdx.x; i < BN; i += kLnThreads) {
-    vecs[i] = p.bias[n_cta + i];
-    vecs[BN + i] = p.gamma[n_cta + i];
-    vecs[2 * BN + i] = p.beta[n_cta + i];
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::cluster_sync_all();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  ptx::grid_dep_wait();
-  ptx::grid_dep_launch();
-
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer (uniform, one elected lane issues)
-    int stage = 0;
-    uint32_t phase = 0;
-    const uint16_t* identity = g_identity64.v[p.h16_fmt == GD_FP16 ? 0 : 1];
-    for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters) {
-      TR(1);
-      for (int kb = 0; kb < k_blocks + kResStages; ++kb) {
-        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * Cfg::kStageBytes;
-        uint8_t* sb = sa + Cfg::kABytes;
-        if (ptx::elect_one()) {
-          if (kb < k_blocks) {
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-            ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kLnBK, m_blk * kLnBM);
-            ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kLnBK, n_cta);
-          } else {                                           // residual stage: [X_hi | X_lo | identity]
-            const int c0 = n_cta + (kb - k_blocks) * kLnBK;
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], 16384 + 16384 + 8192);
-            ptx::tma_load_2d(sa, &tmap_xhi, &full_bar[stage], c0, m_blk * kLnBM);
-            ptx::tma_load_2d(sb, &tmap_xlo, &full_bar[stage], c0, m_blk * kLnBM);
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                             ptx::smem_u32(sb + 16384)),
-                         "l"(identity), "r"(8192), "r"(ptx::smem_u32(&full_bar[stage]))
-                         : "memory");
-          }
-        }
-        __syncwarp();
-        if (++stage == kLnStages) { stage = 0; phase ^= 1; }
-      }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ UMMA issuer (uniform, one elected lane issues)
-    int stage = 0;
-    uint32_t phase = 0;
-    int local = 0;
-    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint32_t smem_u = __shfl_sync(0xffffffffu, ptx::smem_u32(smem), 0);
-    for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
-      const int buf = local & 1;
-      const uint32_t use = (uint32_t)(local >> 1);
-      TR(10);
-      ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);
-      ptx::tc_fence_after();
-      TR(11);
-      const uint32_t tmem_d = tmem_u + (uint32_t)(buf * BN);
-      for (int kb = 0; kb < k_blocks + kResStages; ++kb) {
-        if (kb == k_blocks) TR(12);
-        ptx::mbar_wait(&full_bar[stage], phase);
-        ptx::tc_fence_after();
-        const uint32_t sa = smem_u + (uint32_t)(stage * Cfg::kStageBytes);
-        const uint32_t sb = sa + Cfg::kABytes;
-        if (ptx::elect_one()) {
-          if (kb < k_blocks) {
-#pragma unroll
-            for (int k = 0; k < kLnBK / 16; ++k)
-              ptx::umma_h16(tmem_d, ptx::umma_desc_k_sw128(sa + k * 32), ptx::umma_desc_k_sw128(sb + k * 32), p.idesc,
-                            (kb | k) != 0 ? 1u : 0u);
-          } else {
-            const uint32_t td = tmem_d + (uint32_t)((kb - k_blocks) * kLnBK);
-            const uint32_t si = sb + 16384;
-#pragma unroll
-            for (int k = 0; k < kLnBK / 16; ++k) {
-              ptx::umma_h16(td, ptx::umma_desc_k_sw128(sa + k * 32), ptx::umma_desc_k_sw128(si + k * 32), idesc_res, 1u);
-              ptx::umma_h16(td, ptx::umma_desc_k_sw128(sb + k * 32), ptx::umma_desc_k_sw128(si + k * 32), idesc_res, 1u);
-            }
-          }
-          ptx::umma_commit(&empty_bar[stage]);
-        }
-        __syncwarp();
-        if (++stage == kLnStages) { stage = 0; phase ^= 1; }
-      }
-      if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[buf]);
-      __syncwarp();
-      TR(13);
-    }
-  } else {
-    // ------------------------------------------------------------------ epilogue warps
-    const int ew = warp - 2;
-    const int quarter = warp & 3;
-    const int half = ew >> 2;
-    constexpr int CW = BN / 2;
-    constexpr int NCH = CW / 32;
-    const uint32_t blk0 = ptx::smem_u32(ring) + (uint32_t)ew * 8192u;
-    const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;
-    const uint32_t stats_s = ptx::smem_u32(stats);
-    const uint32_t stats_cl[2] = {ptx::mapa(stats_s, rank), ptx::mapa(stats_s, rank ^ 1u)};
-    const uint32_t sbar_s = ptx::smem_u32(stat_bar);
-    const uint32_t sbar_cl[2] = {ptx::mapa(sbar_s, rank), ptx::mapa(sbar_s, rank ^ 1u)};
-    const uint32_t part = rank * 2u + (uint32_t)half;
-    const int row_in_tile = quarter * 32 + lane;
-    const int n_warp = n_cta + half * CW;
-    int local = 0;
-    for (int m_blk = cluster_id; m_blk < m_tiles; m_blk += n_clusters, ++local) {
-      const int buf = local & 1;
-      const uint32_t use = (uint32_t)(local >> 1);
-      const uint32_t par = (uint32_t)(local & 1);
-      const int m_warp = m_blk * kLnBM + quarter * 32;
-      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * CW);
-      if (ew == 0 && lane == 0) ptx::mbar_arrive_expect_tx(&stat_bar[par], 4 * kLnBM * 8);
-      TR(50);
-      ptx::mbar_wait(&tfull_bar[buf], use & 1);
-      ptx::tc_fence_after();
-      TR(51);
-
-      // ---- pass A (read only): y = acc + bias, running (mean, M2) by Chan's update; TMEM loads one chunk ahead
-      float r_mean = 0.f, r_m2 = 0.f;
-      {
-        uint32_t va[32], vb[32];
-        ptx::tmem_ld_32x32_nowait(taddr0, va);
-        auto pass_a = [&](int c, uint32_t (&vr)[32]) {
-          float v[32];
-          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 b = ptx::lds_v4(vec_s + (c * 32 + q * 4) * 4);
-            v[4 * q] = __uint_as_float(vr[4 * q]) + b.x;
-            v[4 * q + 1] = __uint_as_float(vr[4 * q + 1]) + b.y;
-            v[4 * q + 2] = __uint_as_float(vr[4 * q + 2]) + b.z;
-            v[4 * q + 3] = __uint_as_float(vr[4 * q + 3]) + b.w;
-            s0 += v[4 * q];
-            s1 += v[4 * q + 1];
-            s2 += v[4 * q + 2];
-            s3 += v[4 * q + 3];
-          }
-          const float cm = ((s0 + s1) + (s2 + s3)) * (1.0f / 32.0f);
-          float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float d0 = v[4 * q] - cm, d1 = v[4 * q + 1] - cm, d2 = v[4 * q + 2] - cm, d3 = v[4 * q + 3] - cm;
-            q0 = fmaf(d0, d0, q0);
-            q1 = fmaf(d1, d1, q1);
-            q2 = fmaf(d2, d2, q2);
-            q3 = fmaf(d3, d3, q3);
-          }
-          const float cq = (q0 + q1) + (q2 + q3);
-          const float na = (float)(c * 32), nb = 32.f, nt = na + nb;
-          const float delta = cm - r_mean;
-          r_mean += delta * (nb / nt);
-          r_m2 += cq + delta * delta * (na * nb / nt);
-        };
-        static_assert(NCH == 4, "pass A is unrolled for four 32-column chunks");
-        ptx::tmem_ld_wait_on(va);
-        ptx::tmem_ld_32x32_nowait(taddr0 + 32, vb);
-        pass_a(0, va);
-        ptx::tmem_ld_wait_on(vb);
-        ptx::tmem_ld_32x32_nowait(taddr0 + 64, va);
-        pass_a(1, vb);
-        ptx::tmem_ld_wait_on(va);
-        ptx::tmem_ld_32x32_nowait(taddr0 + 96, vb);
-        pass_a(2, va);
-        ptx::tmem_ld_wait_on(vb);
-        pass_a(3, vb);
-      }
-      {
-        const uint32_t off = ((par * 4u + part) * kLnBM + (uint32_t)row_in_tile) * 8u;
-        ptx::st_async_v2(stats_cl[0] + off, r_mean, r_m2, sbar_cl[0] + par * 8u);
-        ptx::st_async_v2(stats_cl[1] + off, r_mean, r_m2, sbar_cl[1] + par * 8u);
-      }
-      TR(52);
-      ptx::mbar_wait(&stat_bar[par], use & 1);
-      TR(53);
-      float mean = 0.f, m2 = 0.f;
-      {
-        float pm[4], pq[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t a = stats_s + ((par * 4u + (uint32_t)q) * kLnBM + (uint32_t)row_in_tile) * 8u;
-          asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(pm[q]), "=f"(pq[q]) : "r"(a) : "memory");
-          mean += pm[q];
-        }
-        mean *= 0.25f;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) m2 += pq[q] + (float)CW * (pm[q] - mean) * (pm[q] - mean);
-      }
-      const float rstd = rsqrtf(m2 * (1.0f / (float)N) + p.eps);
-      const float shift = -mean * rstd;
-
-      // ---- pass B: normalise from TMEM, hi = round16(z), lo = round16(z - hi), staged in the warp's block c & 1
-#pragma unroll 1
-      for (int c = 0; c < NCH; ++c) {
-        float v[32];
-        ptx::tmem_ld_32x32(taddr0 + c * 32, v);
-        if (c == NCH - 1) {                                  // accumulator buffer fully consumed
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&tempty_bar[buf]);
-        }
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 b2 = ptx::lds_v4(vec_s + (c * 32 + q * 4) * 4);
-          const float4 g = ptx::lds_v4(vec_s + (BN + c * 32 + q * 4) * 4);
-          const float4 b = ptx::lds_v4(vec_s + (2 * BN + c * 32 + q * 4) * 4);
-          v[4 * q] = fmaf(fmaf(v[4 * q] + b2.x, rstd, shift), g.x, b.x);
-          v[4 * q + 1] = fmaf(fmaf(v[4 * q + 1] + b2.y, rstd, shift), g.y, b.y);
-          v[4 * q + 2] = fmaf(fmaf(v[4 * q + 2] + b2.z, rstd, shift), g.z, b.z);
-          v[4 * q + 3] = fmaf(fmaf(v[4 * q + 3] + b2.w, rstd, shift), g.w, b.w);
-        }
-        if (lane == 0) ptx::bulk_wait_read_1();              // the store of chunk c - 2 has read this block
-        __syncwarp();
-        const uint32_t sth = blk0 + (uint32_t)(c & 1) * 4096u, stl = sth + 2048;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint32_t hp[4], lp[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float a = v[8 * q + 2 * e], b = v[8 * q + 2 * e + 1];
-            hp[e] = pack_h16x2(a, b, p.h16_fmt);
-            const float2 f = unpack_h16x2(hp[e], p.h16_fmt);
-            lp[e] = pack_h16x2(a - f.x, b - f.y, p.h16_fmt);
-          }
-          const uint32_t off = (uint32_t)lane * 64 + ((uint32_t)(q ^ ((lane >> 1) & 3)) << 4);
-          ptx::sts_v4u(sth + off, hp[0], hp[1], hp[2], hp[3]);
-          if (p.out_f32) ptx::sts_v4u(stl + off, lp[0], lp[1], lp[2], lp[3]);   // out_f32 holds the lo pointer here
-        }
-        ptx::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0 && !(p.dbg & 2)) {
-          ptx::tma_store_2d(&tmap_ohi, sth, n_warp + c * 32, m_warp);
-          if (p.out_f32) ptx::tma_store_2d(&tmap_olo, stl, n_warp + c * 32, m_warp);
-          ptx::bulk_commit();
-        }
-        TR(60 + c);
-      }
-    }
-    if (lane == 0) ptx::bulk_wait_all();                     // global writes complete before the CTA retires
-    TR(70);
-  }
-
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::cluster_sync_all();
-  if (warp == 2) {
-    ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
-  }
-}
-
-template <int STAGES>
-static int launch_gemm_lnr(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p, const void* res_lo,
-                           cudaStream_t stream) {
-  using Cfg = LnCfg<256, STAGES, true>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GD_CUDA_OK(cudaFuncSetAttribute(gemm_lnr_tcgen05_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    Cfg::kSmemBytes));
-    attr_set = true;
-  }
-  CUtensorMap ta, tw, txh, txl, toh, tol;
-  int rc = make_tmap_2d(&ta, A, p.M, p.K, lda, kLnBM, fmt);
-  if (rc) return rc;
-  rc = make_tmap_2d(&tw, W, 512, p.K, ldw, 256, fmt);
-  if (rc) return rc;
-  rc = make_tmap_2d(&txh, p.residual, p.M, 512, p.ld_res, kLnBM, p.h16_fmt);
-  if (rc) return rc;
-  rc = make_tmap_2d(&txl, res_lo, p.M, 512, p.ld_res, kLnBM, p.h16_fmt);
-  if (rc) return rc;
-  rc = make_tmap_2d_h16_sw64(&toh, p.out_h16, p.M, 512, p.ld_out_h16, 32, p.h16_fmt);
-  if (rc) return rc;
-  tol = toh;
-  if (p.out_f32) {
-    rc = make_tmap_2d_h16_sw64(&tol, p.out_f32, p.M, 512, p.ld_out, 32, p.h16_fmt);
-    if (rc) return rc;
-  }
-  const int sms = num_sms();
-  GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln_split: cannot query the SM count");
-  const int m_tiles = ceil_div(p.M, kLnBM);
-  const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  const uint32_t idesc_res = ptx::umma_idesc_h16_f32(kLnBM, kLnBK, p.h16_fmt == GD_FP16);
-  GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_lnr_tcgen05_kernel<STAGES>, dim3(2 * clusters), dim3(kLnThreads),
-                        Cfg::kSmemBytes, stream, ta, tw, txh, txl, toh, tol, p, idesc_res));
-  GD_LAUNCH_CHECK();
-  return GD_OK;
-}
-
 // MODE 0: p.residual / p.out_f32 are fp32.  MODE 1: p.residual fp32, p.out_f32 carries the lo output (16-bit,
 // leading dimension p.ld_out).  MODE 2: p.residual carries the hi residual and res_lo the lo residual (16-bit,
 // leading dimension p.ld_res), outputs as MODE 1.
@@ -903,7 +530,6 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
   p.out_f32 = out_f32; p.ld_out = ld_out;
   p.out_h16 = out_h16; p.ld_out_h16 = ld_out_h16; p.h16_fmt = h16_fmt;
   p.eps = eps; p.M = M; p.K = K;
-  p.trace = g_ffn_trace;
   {
     static int dbg = -1;
     if (dbg < 0) {
@@ -957,7 +583,6 @@ extern "C" int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, i
   p.out_f32 = out_lo; p.ld_out = ld_out16;
   p.out_h16 = out_hi; p.ld_out_h16 = ld_out16; p.h16_fmt = h16_fmt;
   p.eps = eps; p.M = M; p.K = K;
-  p.trace = g_ffn_trace;
   {
     static int dbg = -1;
     if (dbg < 0) {
@@ -973,17 +598,6 @@ extern "C" int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, i
     const char* e = getenv("GD_LN_SHALLOW_K");
     shallow_k = e ? atoi(e) : 0;
   }
-  // GD_LN_RESMMA=1 (opt-in): pair in / pair out at N = 512 through gemm_lnr_tcgen05_kernel (residual added on the tensor
-  // pipe).  Parity-green; measured 34.5 / 43.9 us against 34.4 / 42.3 us for MODE 2 (K = 512 / 1024): the in-kernel
-  // timeline shows both forms paced by the operand + residual bytes arriving from HBM (13-17 k clocks per tile for 384 KB
-  // = the 25 B/clk an SM's share of the HBM bandwidth delivers), not by the epilogue, so the leaner epilogue buys nothing.
-  static int res_mma = -1;
-  if (res_mma < 0) {
-    const char* e = getenv("GD_LN_RESMMA");
-    res_mma = e ? atoi(e) : 0;
-  }
-  if (N == 512 && split_in && res_mma && h16_fmt == fmt && ld_res16 % 8 == 0)
-    return launch_gemm_lnr<3>(A, lda, W, ldw, fmt, p, res_lo, st);
   if (N == 512 && K <= shallow_k)
     return split_in ? launch_gemm_ln<256, 2, false, 2>(A, lda, W, ldw, fmt, p, res_lo, st)
                     : launch_gemm_ln<256, 2, false, 1>(A, lda, W, ldw, fmt, p, nullptr, st);

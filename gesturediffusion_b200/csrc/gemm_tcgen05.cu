@@ -40,14 +40,14 @@ constexpr int kProducerWarp = kEpiWarps, kMmaWarp = kEpiWarps + 1;
 
 enum { EPI_GENERIC = 0, EPI_BIAS_H16 = 1, EPI_BIAS_GELU_H16 = 2, EPI_BIAS_RES_F32 = 3, EPI_QUAD = 4, EPI_OUT_T = 5 };
 
-// CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x BN tile;
-// each CTA stages its own 128 rows of A and HALF of the W tile, the pair's MMA (M = 256) reads both halves, so the
-// L2 -> SM operand traffic per output element drops by a third (the K = 512 GEMMs are bound by it).
-template <int BN, int CG = 1>
+// One CTA per 128 x BN tile.  (A cta_group::2 variant -- CTA pair per 256 x BN tile, W tile split between the pair --
+// was built and parity-tested in round 1 and measured slower at every encoder shape, 42.1 vs 39.9 us for QKV; it was
+// removed in round 2)
+template <int BN>
 struct GemmCfg {
-  static constexpr int kStages = (CG == 2) ? 6 : ((BN == 256) ? 4 : 6);
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
   static constexpr int kABytes = kBM * kBK * 2;
-  static constexpr int kBBytes = (BN / CG) * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarBytes = 256;
   static constexpr int kStagingBytes = kEpiWarps * 32 * 32 * 4;                 // one 4 KB block per epilogue warp
@@ -93,14 +93,13 @@ __device__ __forceinline__ void prefetch_residual(const gdEpilogue& ep, int lane
   }
 }
 
-template <int BN, int EPI, int CG>
+template <int BN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                          const __grid_constant__ CUtensorMap tmap_out, int M, int N, int K, uint32_t idesc,
                          const gdEpilogue ep, int dbg) {
-  using Cfg = GemmCfg<BN, CG>;
-  const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;      // 0 = pair leader (issues the MMAs)
-  const int n_workers = (int)gridDim.x / CG, worker = (int)blockIdx.x / CG;
+  using Cfg = GemmCfg<BN>;
+  const int n_workers = (int)gridDim.x, worker = (int)blockIdx.x;
   extern __shared__ __align__(1024) uint8_t smem[];          // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment
   uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
   uint8_t* bars = staging + Cfg::kStagingBytes;
@@ -115,7 +114,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   // MMA warp's descriptor arithmetic in the uniform datapath (no ELECT / R2UR waterfall around every UTCHMMA)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int m_tiles = (M + kBM * CG - 1) / (kBM * CG);
+  const int m_tiles = (M + kBM - 1) / kBM;
   const int n_tiles = (N + BN - 1) / BN;
   const int total_tiles = m_tiles * n_tiles;
   const int k_blocks = (K + kBK - 1) / kBK;
@@ -132,17 +131,13 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(&tfull_bar[b], 1);
-      ptx::mbar_init(&tempty_bar[b], kEpiWarps * CG);        // CG == 2: the leader's barrier collects both CTAs
+      ptx::mbar_init(&tempty_bar[b], kEpiWarps);
     }
     ptx::fence_barrier_init();
   }
-  if (warp == 0) {
-    if constexpr (CG == 2) ptx::tmem_alloc_cg2(tmem_slot, Cfg::kTmemCols);
-    else ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
-  }
+  if (warp == 0) ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
   ptx::tc_fence_before();
   __syncthreads();
-  if constexpr (CG == 2) ptx::cluster_sync_all();            // peer barriers initialised, both TMEM allocations done
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   ptx::grid_dep_wait();                                      // prologue above overlaps the previous kernel's tail
@@ -163,13 +158,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           uint8_t* sb = sa + Cfg::kABytes;
           if (ptx::elect_one()) {
             if (dbg & 4) {                                   // diagnostics: no operand traffic
-              if (rank == 0) ptx::mbar_arrive(&full_bar[stage]);
-            } else if constexpr (CG == 2) {
-              // both CTAs' bytes are credited to the LEADER's full barrier (its MMA thread is the only consumer)
-              const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
-              if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
-              ptx::tma_load_2d_cg2(sa, &tmap_a, fb, kb * kBK, (m_blk * 2 + (int)rank) * kBM);
-              ptx::tma_load_2d_cg2(sb, &tmap_w, fb, kb * kBK, n_blk * BN + (int)rank * (BN / 2));
+              ptx::mbar_arrive(&full_bar[stage]);
             } else {
               ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
               ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
@@ -184,7 +173,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   } else if (warp == kMmaWarp) {
     // ------------------------------------------------------------------ UMMA issuer
     // The whole warp runs the loop (uniform control flow, barrier waits by all lanes); one elected lane issues.
-    if (rank == 0) {
+    {
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
@@ -193,8 +182,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
       for (int tile = worker; tile < total_tiles; tile += n_workers, ++local) {
         const int buf = local & 1;
         const uint32_t use = (uint32_t)(local >> 1);
-        if constexpr (CG == 2) ptx::mbar_wait_cluster(&tempty_bar[buf], (use & 1) ^ 1);
-        else ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);     // epilogue drained this accumulator
+        ptx::mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);          // epilogue drained this accumulator
         ptx::tc_fence_after();
         const uint32_t tmem_d = tmem_u + (uint32_t)(buf * BN);
         for (int kb = 0; kb < k_blocks; ++kb) {
@@ -208,20 +196,14 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
               if (dbg & 2) break;                            // diagnostics: no MMAs
               const uint64_t da = ptx::umma_desc_k_sw128(sa + k * kUmmaK * 2);
               const uint64_t db = ptx::umma_desc_k_sw128(sb + k * kUmmaK * 2);
-              if constexpr (CG == 2) ptx::umma_h16_cg2(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-              else ptx::umma_h16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+              ptx::umma_h16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
             }
-            // smem slot reusable when the MMAs retire (in both CTAs of a pair)
-            if constexpr (CG == 2) ptx::umma_commit_cg2(&empty_bar[stage], 3);
-            else ptx::umma_commit(&empty_bar[stage]);
+            ptx::umma_commit(&empty_bar[stage]);             // smem slot reusable when the MMAs retire
           }
           __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        if (ptx::elect_one()) {
-          if constexpr (CG == 2) ptx::umma_commit_cg2(&tfull_bar[buf], 3);     // accumulators complete
-          else ptx::umma_commit(&tfull_bar[buf]);
-        }
+        if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[buf]);     // accumulator complete
         __syncwarp();
       }
     }
@@ -237,7 +219,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
-      const int m_warp = (m_blk * CG + (int)rank) * kBM + quarter * 32;
+      const int m_warp = m_blk * kBM + quarter * 32;
       const int n_base = n_blk * BN + half * kColsPerWarp;
       if (dbg & 1) {                                       // diagnostics: drain without the epilogue work
         ptx::mbar_wait(&tfull_bar[buf], use & 1);
@@ -413,22 +395,6 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
                          pack_h16x2(w[2], w[3], ep.h16_fmt), pack_h16x2(w[4], w[5], ep.h16_fmt),
                          pack_h16x2(w[6], w[7], ep.h16_fmt));
           }
-          if (dbg & 32) {
-            // experiment (GD_GEMM_DBG=32, results right): leave through coalesced generic-proxy stores instead of the
-            // TMA -- 8 lanes read one staged 128-byte row segment back and write it as one full line, 4 rows per
-            // instruction -- so that the stores do not queue behind the producer's operand loads in the TMA unit
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int rl = i * 4 + (lane >> 3), c8 = lane & 7;
-              const uint4 q = ptx::lds_v4u(stg + rl * 128 + ((c8 ^ (rl & 7)) << 4));
-              const int mm = m_warp + rl, n = n0 + c8 * 8;
-              if (mm < M && n < N)
-                *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(ep.out_h16) + (size_t)mm * ep.ld_out_h16 + n) = q;
-            }
-            __syncwarp();
-            continue;
-          }
           ptx::fence_proxy_async();                          // generic-proxy smem writes -> visible to the TMA
           __syncwarp();
           if (lane == 0 && !(dbg & 16)) {
@@ -473,10 +439,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) {
-        if constexpr (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[buf]), 0));
-        else ptx::mbar_arrive(&tempty_bar[buf]);
-      }
+      if (lane == 0) ptx::mbar_arrive(&tempty_bar[buf]);
     }
   }
 
@@ -485,11 +448,9 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if constexpr (CG == 2) ptx::cluster_sync_all();            // the leader's MMAs read the peer's smem until the end
   if (warp == 0) {
     ptx::tc_fence_after();
-    if constexpr (CG == 2) ptx::tmem_dealloc_cg2(tmem_base, Cfg::kTmemCols);
-    else ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
@@ -626,47 +587,31 @@ static int gemm_dbg() {
   return v;
 }
 
-template <int BN, int EPI, int CG = 1>
+template <int BN, int EPI>
 static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int fmt,
                        const gdEpilogue* ep, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, CG>;
+  using Cfg = GemmCfg<BN>;
   static bool attr_set = false;
   if (!attr_set) {
-    GD_CUDA_OK(cudaFuncSetAttribute(gemm_h16_tcgen05_kernel<BN, EPI, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_h16_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::kSmemBytes));
     attr_set = true;
   }
   CUtensorMap ta, tw;
   int rc = make_tmap_2d(&ta, A, M, K, lda, kBM, fmt);
   if (rc) return rc;
-  rc = make_tmap_2d(&tw, W, N, K, ldw, BN / CG, fmt);
+  rc = make_tmap_2d(&tw, W, N, K, ldw, BN, fmt);
   if (rc) return rc;
   CUtensorMap to = tw;                                       // only read by the 16-bit-output epilogues
   if (EPI == EPI_BIAS_H16 || EPI == EPI_BIAS_GELU_H16) {
     rc = make_tmap_2d(&to, ep->out_h16, M, N, ep->ld_out_h16, 32, ep->h16_fmt);
     if (rc) return rc;
   }
-  const int tiles = ceil_div(M, kBM * CG) * ceil_div(N, BN);
-  const int workers = tiles < g_num_sms / CG ? tiles : g_num_sms / CG;
-  const uint32_t idesc = ptx::umma_idesc_h16_f32(kBM * CG, BN, fmt == GD_FP16);
-  if (CG == 1) {
-    GD_CUDA_OK(launch_pdl(PDL_GEMM, gemm_h16_tcgen05_kernel<BN, EPI, CG>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
-                          ta, tw, to, M, N, K, idesc, *ep, gemm_dbg()));
-  } else {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(workers * CG);
-    cfg.blockDim = dim3(kGemmThreads);
-    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CG;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    GD_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_h16_tcgen05_kernel<BN, EPI, CG>, ta, tw, to, M, N, K, idesc, *ep, gemm_dbg()));
-  }
+  const int tiles = ceil_div(M, kBM) * ceil_div(N, BN);
+  const int workers = tiles < g_num_sms ? tiles : g_num_sms;
+  const uint32_t idesc = ptx::umma_idesc_h16_f32(kBM, BN, fmt == GD_FP16);
+  GD_CUDA_OK(launch_pdl(PDL_GEMM, gemm_h16_tcgen05_kernel<BN, EPI>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
+                        ta, tw, to, M, N, K, idesc, *ep, gemm_dbg()));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }
@@ -701,19 +646,8 @@ extern "C" int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ld
   const bool use256 = (N >= 256) && (tiles256 >= 2L * g_num_sms) && (pad256 <= pad128) && bn_env != 128;
   const int epi = pick_epilogue(ep, N);
   cudaStream_t st = (cudaStream_t)stream;
-  // CTA pairs (cta_group::2, 256 x 256 tiles) are implemented and parity-tested but opt-in (GD_GEMM_CG=2): at the
-  // K = 512 encoder shapes they measured 46.6 us vs 41.5 us for QKV (9 tile rounds instead of 8 on 74 pairs, and
-  // the single-CTA kernel is not operand-feed bound: DESIGN.md 4).
-  static int cg_env = -1;
-  if (cg_env < 0) {
-    const char* e = getenv("GD_GEMM_CG");
-    cg_env = (e && e[0] == '2') ? 2 : 1;
-  }
-  const long tiles_pair = (long)ceil_div(M, 2 * kBM) * ceil_div(N, 256);
-  const bool pair = use256 && cg_env == 2 && tiles_pair >= 2L * (g_num_sms / 2);
 #define GD_GEMM_CASE(E)                                                                    \
   case E:                                                                                  \
-    if (pair) return launch_gemm<256, E, 2>(A, lda, W, ldw, M, N, K, fmt, ep, st);         \
     return use256 ? launch_gemm<256, E>(A, lda, W, ldw, M, N, K, fmt, ep, st)              \
                   : launch_gemm<128, E>(A, lda, W, ldw, M, N, K, fmt, ep, st);
   switch (epi) {

@@ -345,45 +345,6 @@ __device__ __forceinline__ void mbar_arrive_expect_tx_s(uint32_t addr, uint32_t 
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(addr), "r"(bytes) : "memory");
 }
 
-// ---------------------------------------------------------------- CTA-pair (cta_group::2) variants
-// One warp of EACH CTA of the pair executes alloc / dealloc.
-__device__ __forceinline__ void tmem_alloc_cg2(uint32_t* smem_slot, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
-               "r"(ncols)
-               : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc_cg2(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// TMA load into THIS CTA's shared memory whose completion bytes are credited to an mbarrier given as a
-// shared::cluster address (the pair leader's full barrier).
-__device__ __forceinline__ void tma_load_2d_cg2(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr,
-                                                int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
-      : "memory");
-}
-// D[tmem of both CTAs] (+)= A * B^T with M = 256 (128 rows per CTA), B split along N between the two CTAs'
-// shared memories; issued by one thread of the leader CTA, descriptors hold the leader's smem offsets.
-__device__ __forceinline__ void umma_h16_cg2(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                              uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// commit of the pair's MMAs: arrives on the mbarrier at this offset in every CTA of `cta_mask`.
-__device__ __forceinline__ void umma_commit_cg2(uint64_t* bar, uint16_t cta_mask) {
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-                   smem_u32(bar)),
-               "h"(cta_mask)
-               : "memory");
-}
-
 // Shared-memory descriptor for an MN-major 16-bit operand in the 128-byte-swizzled layout that a TMA box of
 // [64 elements (MN, contiguous) x rows (K)] produces: atoms of 64 (MN) x 8 (K) elements = 8 rows of 128 B;
 // SBO = byte distance between 8-row K groups (1024), LBO = byte distance between 64-element MN groups

@@ -112,16 +112,6 @@ class DenoiserEngine:
         # batches) the two GEMM kernels, which spread N over the SMs, are faster (batch 1 x 196 frames: 0.40 vs 0.50 ms per
         # denoise step; break-even near 25 row tiles, profiles/r01g_sweep.md)
         self.fuse_ffn_min_rows = int(os.environ.get("GD_FUSE_FFN_MIN_ROWS", "4096"))
-        # The encoder stack of the two guidance branches (or of two halves of the batch) as two independent kernel
-        # chains on two streams: a persistent kernel's last, partly filled round of tiles (197 row tiles over 74
-        # clusters = 2.66 -> 3 rounds at the cfg2a shapes) then overlaps the other chain's next kernel.
-        self.split_streams = os.environ.get("GD_SPLIT_STREAMS", "0") == "1"
-        self._side_stream = None
-        # GD_L2_WINDOW=1 (opt-in): the residual-stream pair as a persisting L2 access-policy window on every tcgen05 launch
-        # (gd_set_l2_window).  Measured on a B200 (79 MB maximum carve-out of the 126 MB L2): cfg2a (51.6 MB pair) 1.510 vs
-        # 1.517 ms per denoise step, cfg3 (63.4 MB pair) 2.089 vs 1.936 ms -- the carve-out starves the QKV / H / ATT
-        # producer-consumer pairs the ordinary replacement policy already serves, so it stays off.
-        self.l2_window = os.environ.get("GD_L2_WINDOW", "0") == "1"
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -227,7 +217,7 @@ class DenoiserEngine:
         ws["a_in"] = buf(B * T, _round_up(self.k_in, 8), dtype=act)
         ws["X32"] = buf(R, d)
         if self.h16:
-            # the residual stream as a 16-bit (hi, lo) pair in ONE allocation: a single L2 persisting window covers it
+            # the residual stream as a 16-bit (hi, lo) pair in one allocation
             ws["Xpair"] = buf(2, R, d, dtype=act)
             ws["Xa"], ws["Xlo"] = ws["Xpair"][0], ws["Xpair"][1]
         else:
@@ -248,14 +238,6 @@ class DenoiserEngine:
         self._ws[key] = ws
         return ws
 
-    def apply_l2_window(self, ws):
-        """Host-side launch-attribute state for the kernels that follow (call outside stream capture)."""
-        if self.h16 and self.l2_window and "Xpair" in ws:
-            ws["l2_granted"] = K.set_l2_window(ws["Xpair"])
-        elif ws.get("l2_granted"):
-            K.set_l2_window(None)
-            ws["l2_granted"] = 0
-
     def _outs(self, t):
         """Epilogue output kwargs for an `act` buffer."""
         return dict(out_h16=t) if t.dtype != torch.float32 else dict(out_f32=t)
@@ -268,7 +250,6 @@ class DenoiserEngine:
         W_c.seed_emb (V2).  `branches` is a list of bools: uncond flag per batched branch."""
         B, T, nb, d, J = ws["B"], ws["T"], ws["nb"], self.d, self.J
         w = self.w
-        self.apply_l2_window(ws)
         assert len(branches) == nb
         seed = y["seed"].to(self.device, torch.float32)
         if tuple(seed.shape) != (B, J, 1, self.n_seed):
@@ -328,21 +309,7 @@ class DenoiserEngine:
             rc, rs = self.rope_tables(T)
             K.local_attention(ws["XL"], rc, rs, X32, xa_b, nb * B, T, d, self.cl_head, 10)
         n_seq = nb * B
-        if self.split_streams and n_seq >= 2 and self.h16:
-            # two independent halves of the sequences (the two guidance branches when nb == 2), forked onto a side
-            # stream and joined before OutputProcess; rows of a half are contiguous in every workspace buffer
-            h0 = n_seq // 2
-            main = torch.cuda.current_stream()
-            if self._side_stream is None:
-                self._side_stream = torch.cuda.Stream(device=self.device)
-            side = self._side_stream
-            side.wait_stream(main)
-            self._encoder_stack(ws, 0, h0, S)
-            with torch.cuda.stream(side):
-                self._encoder_stack(ws, h0, n_seq, S)
-            main.wait_stream(side)
-        else:
-            self._encoder_stack(ws, 0, n_seq, S)
+        self._encoder_stack(ws, 0, n_seq, S)
         # OutputProcess + output[1:] + permute to [.,J,1,T] (mdm.py:219-222,372-380)
         K.gemm(Xa, w["out.w"], K.epilogue(bias=w["out.b"], out_t=ws["OUT"], t_s=S, t_t=T, t_skip=1), K=d)
 
@@ -393,13 +360,10 @@ class DenoiserEngine:
 
     def kernels_per_step(self, rows):
         """Kernel launches of one denoiser evaluation over `rows` token rows (nb * B * S)."""
-        split = self.split_streams and self.h16              # one chain per half of the sequences (n_seq >= 2)
         per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512)) else 7
         if (per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512
-                and self.F % 256 == 0 and (rows // 2 if split else rows) >= self.fuse_ffn_min_rows):
+                and self.F % 256 == 0 and rows >= self.fuse_ffn_min_rows):
             per_layer = 4
-        if split:
-            per_layer *= 2
         return 2 + (1 if self.arch == "v2" else 0) + per_layer * self.L + 1
 
     def flops_per_step(self, B, T, nb):

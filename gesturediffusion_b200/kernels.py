@@ -173,20 +173,6 @@ def ffn_ln_split(x_hi, x_lo, w1, b1, w2, b2, gamma, beta, out_hi, out_lo=None, e
     _cabi.check(rc, "gd_ffn_h16_ln_split")
 
 
-def set_l2_window(t=None):
-    """Keep tensor `t` (the residual-stream pair) resident in L2 for the tcgen05 kernels launched afterwards
-    (persisting access-policy window); None turns the hint off.  Returns the persisting-L2 carve-out in bytes."""
-    import ctypes
-    lib = _cabi.load()
-    granted = ctypes.c_int64(0)
-    if t is None:
-        rc = lib.gd_set_l2_window(None, 0, ctypes.byref(granted))
-    else:
-        rc = lib.gd_set_l2_window(_dev(t, t.dtype, "window"), t.numel() * t.element_size(), ctypes.byref(granted))
-    _cabi.check(rc, "gd_set_l2_window")
-    return int(granted.value)
-
-
 def attention(qkv, out, n_seq, S, n_heads, head_dim):
     lib = _cabi.load()
     with _Timed("attention", n_seq=n_seq, S=S, H=n_heads, dh=head_dim):

@@ -119,12 +119,6 @@ int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t ld_x, const 
                         int32_t F, int32_t fmt, const float* gamma, const float* beta, float eps,
                         void* out_hi, void* out_lo, int32_t ld_out, void* stream);
 
-/* L2 residency hint for the residual stream (new; the reference has no counterpart): [base, base + bytes) becomes a
- * persisting access-policy window on every tcgen05 GEMM / GEMM+LayerNorm / attention launch that follows, so the
- * (hi, lo) residual pair -- read by four kernels and rewritten in place by two per encoder layer -- stays in the 126 MB
- * L2 instead of travelling through HBM.  bytes = 0 turns it off.  *granted (may be NULL) receives the persisting-L2
- * carve-out that was set.  Host-side state; call outside stream capture. */
-int gd_set_l2_window(void* base, int64_t bytes, int64_t* granted);
 
 /* Debug aid (tools/trace_ffn.py): device buffer of >= 3 * 4096 uint64 that CTA 0 of every later
  * gd_ffn_h16_ln_split launch fills with (tag << 48 | SM clock) records; NULL (default) turns it off. */

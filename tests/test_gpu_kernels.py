@@ -394,45 +394,6 @@ def test_ffn_ln_split_repeatable_under_load_and_argument_checks(cuda_device):
         Kn.ffn_ln_split(hi, lo, w1[:384], b1[:384], w2[:, :384], b2, gamma, beta, out_hi=torch.zeros_like(hi))
 
 
-def test_gemm_ln_split_tensor_pipe_residual_variant(cuda_device):
-    """GD_LN_RESMMA=1 (read once per process, hence the subprocess): gemm_lnr_tcgen05_kernel -- the pair-in / pair-out
-    GEMM + LayerNorm with the residual added by identity MMAs -- against float64 and against the default kernel."""
-    import os
-    import subprocess
-    import sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    code = r"""
-import math, sys, torch
-sys.path.insert(0, %r)
-from gesturediffusion_b200 import kernels as K
-def rel(a, b): return float((a.double() - b.double()).norm() / b.double().norm())
-for dt, tol in ((torch.float16, 5e-6), (torch.bfloat16, 3e-5)):
-    for M, Kd in ((1, 512), (300, 512), (25216 - 37, 1024)):
-        g = torch.Generator(device="cuda").manual_seed(M)
-        a = torch.randn(M, Kd, device="cuda", generator=g).to(dt)
-        w = (torch.randn(512, Kd, device="cuda", generator=g) / math.sqrt(Kd)).to(dt)
-        bias, gamma, beta = (torch.randn(512, device="cuda", generator=g) for _ in range(3))
-        x = torch.randn(M, 512, device="cuda", generator=g) * 2 + 0.5
-        hi = x.to(dt); lo = (x - hi.float()).to(dt)
-        ref = torch.nn.functional.layer_norm(hi.double() + lo.double() + a.double() @ w.double().t() + bias.double(),
-                                             (512,), gamma.double(), beta.double(), 1e-5)
-        oh, ol = torch.zeros_like(hi), torch.zeros_like(lo)
-        K.gemm_ln_split(a, w, bias, gamma, beta, out_hi=oh, out_lo=ol, res_hi=hi, res_lo=lo)
-        assert rel(oh.float() + ol.float(), ref) < tol, (dt, M, Kd, rel(oh.float() + ol.float(), ref))
-        h2, l2 = hi.clone(), lo.clone()
-        K.gemm_ln_split(a, w, bias, gamma, beta, out_hi=h2, out_lo=l2, res_hi=h2, res_lo=l2)     # in place
-        assert torch.equal(h2, oh) and torch.equal(l2, ol)
-        h3 = torch.zeros_like(hi)
-        K.gemm_ln_split(a, w, bias, gamma, beta, out_hi=h3, res_hi=hi, res_lo=lo)                # hi only
-        assert torch.equal(h3, oh)
-print("RESMMA-OK")
-""" % root
-    env = dict(os.environ, GD_LN_RESMMA="1")
-    r = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
-                       timeout=300)
-    assert r.returncode == 0 and "RESMMA-OK" in r.stdout, r.stdout[-2000:]
-
-
 def test_gemm_ln_rejects_other_widths(cuda_device):
     from gesturediffusion_b200 import _cabi
     Kn = _K()

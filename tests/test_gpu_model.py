@@ -93,29 +93,6 @@ def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
     assert rel_l2(fused, base) < TOL[precision]
 
 
-@pytest.mark.parametrize("case", ["v1_humanml", "v2_gesture", "v1_small"])
-def test_forward_two_stream_split_is_bit_exact(cuda_device, case):
-    """GD_SPLIT_STREAMS: the encoder stack of the two halves of the sequences as two kernel chains on two streams
-    gives exactly the single-chain result (same kernels on row ranges; rows never interact across sequences)."""
-    from gesturediffusion_b200 import ClassifierFreeSampleModel
-    cfg, sd, x, y, gold = load_model_case(case)
-    m = build_product_model(cfg, sd, cuda_device, "fp16")
-    xd, yd, t = x.to(cuda_device), to_dev(y, cuda_device), gold["t"].to(cuda_device)
-    cfgm = ClassifierFreeSampleModel(m)
-    eng = m.engine()
-    saved = eng.split_streams
-    try:
-        eng.split_streams = False
-        base = cfgm(xd, t, yd).clone()
-        eng.split_streams = True
-        split = cfgm(xd, t, yd).clone()
-    finally:
-        eng.split_streams = saved
-    torch.cuda.synchronize()
-    assert torch.equal(split, base)
-    assert rel_l2(split, gold["guided"]) < GUIDED_TOL["fp16"]
-
-
 def test_v2_rejects_length_not_multiple_of_window(cuda_device):
     cfg, sd, x, y, gold = load_model_case("v2_small")
     m = build_product_model(cfg, sd, cuda_device, "fp32")

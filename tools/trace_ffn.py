@@ -15,7 +15,6 @@ from gesturediffusion_b200 import _cabi, kernels as K  # noqa: E402
 
 
 def main():
-    which = sys.argv[sys.argv.index("--kernel") + 1] if "--kernel" in sys.argv else "ffn"
     dev = torch.device("cuda", 0)
     M, d, F = 25216, 512, 1024
     g = torch.Generator(device=dev).manual_seed(0)
@@ -24,15 +23,9 @@ def main():
     w1, w2 = rnd(F, d, sc=0.04), rnd(d, F, sc=0.03)
     b1, b2, gam, bet = (rnd(n, dt=torch.float32) for n in (F, d, d, d))
     oh, ol = torch.empty_like(hi), torch.empty_like(lo)
-    att, hh = rnd(M, d), rnd(M, F)
 
     def run():
-        if which == "ffn":
-            K.ffn_ln_split(hi, lo, w1, b1, w2, b2, gam, bet, out_hi=oh, out_lo=ol)
-        elif which == "lnr":       # out_proj + residual + LayerNorm, tags 1 / 10-13 / 50-53, 60-63, 70
-            K.gemm_ln_split(att, w2[:, :d].contiguous(), b2, gam, bet, out_hi=oh, out_lo=ol, res_hi=hi, res_lo=lo)
-        else:                      # "lnr2": linear2 + residual + LayerNorm (K = 1024)
-            K.gemm_ln_split(hh, w2, b2, gam, bet, out_hi=oh, out_lo=ol, res_hi=hi, res_lo=lo)
+        K.ffn_ln_split(hi, lo, w1, b1, w2, b2, gam, bet, out_hi=oh, out_lo=ol)
     for _ in range(3):
         run()
     buf = torch.zeros(3 * 4096, dtype=torch.int64, device=dev)
