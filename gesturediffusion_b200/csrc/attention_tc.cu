@@ -336,11 +336,16 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 // ---------------------------------------------------------------------------- host side
 // Returns GD_ERR_UNSUPPORTED (without setting an error) when the shape is outside this kernel's range so
 // that gd_attention_h16 can fall back to its mma.sync flash kernel (other head dims, S > 256).
+// S <= 256: this file's kernel (a whole row of scores in TMEM); longer sequences: attention_tc_long.cu (keys in
+// blocks of 128, online softmax) -- up to the encoder's positional table (5000 rows, mdm.py:277) and beyond.
 bool attention_tc_supported(int S, int n_heads, int head_dim) {
-  return head_dim == 128 && S >= 1 && S <= 256 && n_heads >= 1;
+  return head_dim == 128 && S >= 1 && n_heads >= 1;
 }
 
+int launch_attention_tc_long(const void* qkv, void* out, int n_seq, int S, int n_heads, int fmt, cudaStream_t stream);
+
 int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_heads, int fmt, cudaStream_t stream) {
+  if (S > 256) return launch_attention_tc_long(qkv, out, n_seq, S, n_heads, fmt, stream);
   static bool attr_set = false;
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemBytes));

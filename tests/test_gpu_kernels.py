@@ -168,6 +168,39 @@ def test_attention(cuda_device, n_seq, S, H, dh, dtype):
     assert rel_l2(out.float(), ref) < {"fp32": 2e-6, "bf16": 6e-3, "fp16": 8e-4}[dtype]
 
 
+# S > 256 at head_dim 128: the tcgen05 kernel with the keys in blocks of 128 and an online softmax
+# (attention_tc_long.cu).  257 = one key in the third block; 301 / 401 / 601 = the 300 / 400 / 600-frame sweep rows
+# (odd / even / odd number of query tiles: idle second slot in the last pair); 1000 = 8 blocks; 160 sequences x 4 heads
+# x 3 pairs = several items per CTA (ring and phase bookkeeping across items); large scores exercise the rescale.
+@pytest.mark.parametrize("n_seq,S,H,scale", [(3, 257, 4, 1.0), (5, 301, 4, 1.0), (2, 401, 4, 1.0), (3, 601, 4, 1.0),
+                                             (2, 1000, 2, 1.0), (160, 601, 4, 1.0), (7, 384, 1, 1.0), (4, 601, 4, 4.0)])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16"])
+def test_attention_long_sequences(cuda_device, n_seq, S, H, scale, dtype):
+    Kn = _K()
+    dh = 128
+    d = H * dh
+    g = torch.Generator(device="cuda").manual_seed(S + n_seq)
+    qkv = torch.randn(n_seq * S, 3 * d, device="cuda", generator=g)
+    qkv[:, :2 * d] *= scale                                  # larger |q.k|: sharper rows, the running maximum moves
+    tdt = TDT[dtype]
+    qkv = qkv.to(tdt)
+    out = torch.full((n_seq * S, d), 7.0, device="cuda", dtype=tdt)
+    Kn.attention(qkv, out, n_seq, S, H, dh)
+    out2 = torch.full_like(out, -3.0)
+    Kn.attention(qkv, out2, n_seq, S, H, dh)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)                            # every element written, repeatable
+    errs = []
+    for s0 in range(0, n_seq, 16):                           # reference in slices (float64 scores of 160 x 601^2 x 4)
+        s1 = min(n_seq, s0 + 16)
+        blk = qkv[s0 * S:s1 * S].double().view(s1 - s0, S, 3, H, dh).permute(2, 0, 3, 1, 4)
+        ref = torch.softmax(blk[0] @ blk[1].transpose(-1, -2) / math.sqrt(dh), dim=-1) @ blk[2]
+        ref = ref.permute(0, 2, 1, 3).reshape((s1 - s0) * S, d)
+        errs.append(rel_l2(out[s0 * S:s1 * S].float(), ref))
+    record_parity("attention long n_seq=%d S=%d H=%d x%.0f %s: rel-L2 %.2e" % (n_seq, S, H, scale, dtype, max(errs)))
+    assert max(errs) < {"bf16": 6e-3, "fp16": 8e-4}[dtype]
+
+
 @pytest.mark.parametrize("rows,d", [(1, 128), (1000, 512), (777, 1024)])
 def test_layernorm(cuda_device, rows, d):
     Kn = _K()
