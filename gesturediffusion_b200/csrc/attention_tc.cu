@@ -345,7 +345,15 @@ bool attention_tc_supported(int S, int n_heads, int head_dim) {
 int launch_attention_tc_long(const void* qkv, void* out, int n_seq, int S, int n_heads, int fmt, cudaStream_t stream);
 
 int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_heads, int fmt, cudaStream_t stream) {
-  if (S > 256) return launch_attention_tc_long(qkv, out, n_seq, S, n_heads, fmt, stream);
+  {
+    static int long_min = -1;                                // GD_ATT_LONG_MIN (experiments): smallest S on the block-wise kernel
+    if (long_min < 0) {
+      const char* e = getenv("GD_ATT_LONG_MIN");
+      long_min = e ? atoi(e) : 257;
+      if (long_min > 257 || long_min < 1) long_min = 257;
+    }
+    if (S >= long_min) return launch_attention_tc_long(qkv, out, n_seq, S, n_heads, fmt, stream);
+  }
   static bool attr_set = false;
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemBytes));
