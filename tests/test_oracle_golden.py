@@ -61,3 +61,20 @@ def test_oracle_matches_live_reference():
         ref = m(x, gold["t"], y)
     assert rel_l2(make_model_fn(sd, cfg)(x, gold["t"], y), ref) < FP32_TOL
     assert rel_l2(ref, gold["cond"]) == 0.0          # fixtures are reproducible from the committed script
+
+
+def test_staged_reference_archive_is_the_reference():
+    """oracle/_ref/reference_path.zip (written by oracle/stage_ref.py, git-ignored, travels to the GPU box) holds
+    byte-identical copies of the reference modules the sampling path imports: every archived file has its manifest
+    digest and -- where /root/reference exists -- equals the source file."""
+    import os
+    from oracle import stage_ref
+    if not os.path.exists(os.path.join(stage_ref.DEST, stage_ref.ARCHIVE)):
+        pytest.skip("oracle/_ref not staged (run __graft_entry__.build() where /root/reference exists)")
+    src = stage_ref.SRC if os.path.isdir(os.path.join(stage_ref.SRC, "diffusion")) else None
+    assert stage_ref.verify(src=src)
+    import json
+    man = json.load(open(os.path.join(stage_ref.DEST, "MANIFEST.json")))["files"]
+    for needed in ("diffusion/gaussian_diffusion.py", "diffusion/respace.py", "model/mdm.py", "model/mdm_old.py",
+                   "model/cfg_sampler.py", "model/local_attention.py"):
+        assert needed in man, needed

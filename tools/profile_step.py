@@ -36,7 +36,7 @@ def main():
     from gesturediffusion_b200.synthetic import build_model, make_inputs
     _cabi.load()
     dev = torch.device("cuda", 0)
-    cfg, sd, B, T = bench.build_case(a)
+    cfg, sd, B, T = bench.build_case(a.workload, a.batch)
     den = build_model(cfg, sd, dev, a.precision)
     model = den if a.no_cfg else ClassifierFreeSampleModel(den)
     dif = create_gaussian_diffusion(timestep_respacing=[a.chain])
