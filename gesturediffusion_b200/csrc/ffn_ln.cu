@@ -38,7 +38,11 @@
 // by its dependency chain (GEMM1 -> GELU -> exchange -> GEMM2 -> LayerNorm tail on ONE set of epilogue warps with a
 // single-buffered output accumulator), not by the feed.  The GELU arithmetic is issue-bound: the 9-instruction
 // gelu_fast took the kernel from 71 to 66 us.  Replacing pass B's TMA stores by coalesced generic stores was slower
-// (pass B 8.2 k vs 7.7 k clocks, kernel 71 vs 66 us) and was dropped.
+// (pass B 8.2 k vs 7.7 k clocks, kernel 71 vs 66 us) and was dropped; so was a ring of three 2 KB staging pieces with
+// three TMA stores in flight per warp (pass B 6.2-6.8 k clocks, kernel 68.3 us: no gain, profiles/r02k_trace_ffn_ring.txt)
+// -- pass B costs about 5.7 k clocks without any store (GD_FFN_DBG=2): 4 x (TMEM load, 24 LDS.128, ~150 FP / convert
+// instructions, fence.proxy.async) on eight warps is latency-bound, and the single-buffered output accumulator keeps it on
+// the tile's critical path.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -65,14 +69,8 @@ constexpr int kFfHbufOff = kFfStages * kFfStageBytes;
 constexpr int kFfLnOff = kFfHbufOff + 2 * kFfSlotBytes;            // dedicated 4 KB block per epilogue warp
 constexpr int kFfI64Off = kFfLnOff + (kFfDedicatedLn ? kFfEpiWarps * 4096 : 0);           // 64 x 64 identity, K-major 128B swizzle (8 KB)
 constexpr int kFfVecOff = kFfI64Off + 8192;                        // b2 | gamma | beta slices of this CTA
-// Statistics exchange: [part][row] (mean, M2), ONE copy.  A CTA's partials of tile t + 1 can only arrive after its peer's
-// eight epilogue warps have all left the tail of tile t: they are sent after y_full(t + 1), i.e. after every GEMM2 of
-// t + 1, which needs the peer's H chunks of t + 1, each of which all eight peer warps write after their tail of t.
-constexpr int kFfStatOff = kFfVecOff + 3 * kFfBN * 4;
-// Third 2 KB staging piece per epilogue warp for pass B (pieces 0 / 1 are the two halves of the warp's H slab): three
-// TMA stores in flight per warp instead of waiting for each store's shared-memory read before staging the next.
-constexpr int kFfPieceOff = kFfStatOff + 4 * kFfBM * 8;
-constexpr int kFfBarOff = kFfPieceOff + kFfEpiWarps * 2048;
+constexpr int kFfStatOff = kFfVecOff + 3 * kFfBN * 4;              // [parity][part][row] (mean, M2)
+constexpr int kFfBarOff = kFfStatOff + 2 * 4 * kFfBM * 8;
 constexpr int kFfSmemBytes = kFfBarOff + 512;
 
 struct FfParams {
@@ -502,7 +500,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
 
       // ---- exchange of the four partial (mean, M2) of every row (2 column halves x 2 CTAs)
       {
-        const uint32_t off = (part * kFfBM + (uint32_t)row_in_tile) * 8u;
+        const uint32_t off = ((par * 4u + part) * kFfBM + (uint32_t)row_in_tile) * 8u;
         ptx::st_async_v2(stats_cl[0] + off, r_mean, r_m2, sbar_cl[0] + par * 8u);
         ptx::st_async_v2(stats_cl[1] + off, r_mean, r_m2, sbar_cl[1] + par * 8u);
       }
@@ -517,7 +515,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         float pm[4], pq[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const uint32_t a = stats_s + ((uint32_t)q * kFfBM + (uint32_t)row_in_tile) * 8u;
+          const uint32_t a = stats_s + ((par * 4u + (uint32_t)q) * kFfBM + (uint32_t)row_in_tile) * 8u;
           asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(pm[q]), "=f"(pq[q]) : "r"(a) : "memory");
           mean += pm[q];
         }
@@ -528,11 +526,7 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
       const float rstd = rsqrtf(m2 * (1.0f / (float)kFfD) + p.eps);
       const float shift = -mean * rstd;
 
-      // ---- pass B: normalise from TMEM, hi = round16(z), lo = round16(z - hi).  Every 32-column chunk leaves as two TMA
-      // stores (hi, lo) of a [32 rows x 64 B] box each, staged in a ring of three 2 KB pieces; one bulk group per store,
-      // so a piece is rewritten when the store issued three pieces earlier has read it (wait_group.read 2).
-      const uint32_t piece2 = ptx::smem_u32(smem + kFfPieceOff) + (uint32_t)ew * 2048u;
-      int pk_i = 0;                                          // ring position
+      // ---- pass B: normalise from TMEM, hi = round16(z), lo = round16(z - hi), staged in block c & 1
 #pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
         float v[32];
@@ -552,36 +546,32 @@ ffn_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           v[4 * q + 2] = fmaf(fmaf(v[4 * q + 2] + b2.z, rstd, shift), g.z, b.z);
           v[4 * q + 3] = fmaf(fmaf(v[4 * q + 3] + b2.w, rstd, shift), g.w, b.w);
         }
-        uint32_t hp[16];
+        if (lane == 0) {                                     // the block's previous store has read it
+          if (kFfDedicatedLn) ptx::bulk_wait_read_1();
+          else ptx::bulk_wait_read_all();
+        }
+        __syncwarp();
+        const uint32_t sth = blk(c), stl = sth + 2048;
 #pragma unroll
-        for (int e = 0; e < 16; ++e) hp[e] = pack_h16x2(v[2 * e], v[2 * e + 1], p.h16_fmt);
+        for (int q = 0; q < 4; ++q) {
+          uint32_t hp[4], lp[4];
 #pragma unroll
-        for (int pass = 0; pass < 2; ++pass) {
-          if (pass == 1 && !p.has_lo) break;
-          if (lane == 0) ptx::bulk_wait_read_2();            // the store that used this piece has read it
-          __syncwarp();
-          const uint32_t st = pk_i == 0 ? slab : (pk_i == 1 ? slab + 2048u : piece2);
-          pk_i = pk_i == 2 ? 0 : pk_i + 1;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              if (pass == 0) {
-                w[e] = hp[4 * q + e];
-              } else {
-                const float2 f = unpack_h16x2(hp[4 * q + e], p.h16_fmt);
-                w[e] = pack_h16x2(v[8 * q + 2 * e] - f.x, v[8 * q + 2 * e + 1] - f.y, p.h16_fmt);
-              }
-            }
-            ptx::sts_v4u(st + (uint32_t)lane * 64 + ((uint32_t)(q ^ ((lane >> 1) & 3)) << 4), w[0], w[1], w[2], w[3]);
+          for (int e = 0; e < 4; ++e) {
+            const float a = v[8 * q + 2 * e], b = v[8 * q + 2 * e + 1];
+            hp[e] = pack_h16x2(a, b, p.h16_fmt);
+            const float2 f = unpack_h16x2(hp[e], p.h16_fmt);
+            lp[e] = pack_h16x2(a - f.x, b - f.y, p.h16_fmt);
           }
-          ptx::fence_proxy_async();
-          __syncwarp();
-          if (lane == 0 && !(p.dbg & 2)) {
-            ptx::tma_store_2d(pass == 0 ? &tmap_ohi : &tmap_olo, st, n_warp + c * 32, m_warp);
-            ptx::bulk_commit();
-          }
+          const uint32_t off = (uint32_t)lane * 64 + ((uint32_t)(q ^ ((lane >> 1) & 3)) << 4);
+          ptx::sts_v4u(sth + off, hp[0], hp[1], hp[2], hp[3]);
+          if (p.has_lo) ptx::sts_v4u(stl + off, lp[0], lp[1], lp[2], lp[3]);
+        }
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0 && !(p.dbg & 2)) {
+          ptx::tma_store_2d(&tmap_ohi, sth, n_warp + c * 32, m_warp);
+          if (p.has_lo) ptx::tma_store_2d(&tmap_olo, stl, n_warp + c * 32, m_warp);
+          ptx::bulk_commit();
         }
       }
       TR(54);
