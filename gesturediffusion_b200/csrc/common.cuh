@@ -35,14 +35,16 @@ extern unsigned long long* g_ffn_trace;     // debug timeline buffer (gd_ffn_tra
   } while (0)
 
 // GD_PDL=0 turns programmatic dependent launch off (kernels then serialise the ordinary way).
-// GD_PDL is a bit mask over kernel kinds: 1 plain GEMM, 2 GEMM+LayerNorm, 4 attention.  Default 6: measured on the
-// cfg2a step (ms per denoise step, same box): none 1.698, all 1.681, GEMM only 1.707, GEMM+LN and attention 1.671.
-enum { PDL_GEMM = 1, PDL_GEMM_LN = 2, PDL_ATTENTION = 4 };
+// GD_PDL is a bit mask over kernel kinds: 1 plain GEMM with at least one tile per SM, 2 GEMM+LayerNorm, 4 attention,
+// 8 plain GEMM with fewer tiles than SMs (small batches).  Default 14: measured on the cfg2a step (ms per denoise step,
+// same box): none 1.698, all 1.681, large GEMM only 1.707, GEMM+LN and attention 1.671; on the batch-1 step (cfg1, every
+// GEMM is "small"): 0.354 with the GEMMs included against 0.365 without and 0.394 with none (profiles/r02k_cfg1_pdl.txt).
+enum { PDL_GEMM = 1, PDL_GEMM_LN = 2, PDL_ATTENTION = 4, PDL_GEMM_SMALL = 8 };
 inline bool pdl_enabled(int kind) {
   static int mask = -1;
   if (mask < 0) {
     const char* e = getenv("GD_PDL");
-    mask = e ? atoi(e) : 6;
+    mask = e ? atoi(e) : 14;
   }
   return (mask & kind) != 0;
 }

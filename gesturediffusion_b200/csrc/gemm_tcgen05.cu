@@ -610,7 +610,7 @@ static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, in
   const int tiles = ceil_div(M, kBM) * ceil_div(N, BN);
   const int workers = tiles < g_num_sms ? tiles : g_num_sms;
   const uint32_t idesc = ptx::umma_idesc_h16_f32(kBM, BN, fmt == GD_FP16);
-  GD_CUDA_OK(launch_pdl(PDL_GEMM, gemm_h16_tcgen05_kernel<BN, EPI>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
+  GD_CUDA_OK(launch_pdl(tiles < g_num_sms ? PDL_GEMM_SMALL : PDL_GEMM, gemm_h16_tcgen05_kernel<BN, EPI>, dim3(workers), dim3(kGemmThreads), Cfg::kSmemBytes, stream,
                         ta, tw, to, M, N, K, idesc, *ep, gemm_dbg()));
   GD_LAUNCH_CHECK();
   return GD_OK;
