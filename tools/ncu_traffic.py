@@ -62,17 +62,20 @@ def main():
     traffic = {"_about": "per launch, from an ncu --set full capture of consecutive launches of one encoder layer inside "
                          "the second denoise step of tools/profile_step.py (cfg2a); regenerate with tools/ncu_traffic.py",
                "_source": os.path.relpath(path, ROOT)}
-    print("| kernel | duration us | dram read MB | dram write MB | dram total / algorithmic | L2->SM MB (lts__t_bytes) | "
+    print("| kernel | duration us | dram read MB | dram write MB | dram total / algorithmic | L2->SM MB (l1tex__m_xbar2l1tex_read_bytes) | "
           "L2->SM / algorithmic | L2 hit % | tensor pipe % (active) |")
     print("|---|---|---|---|---|---|---|---|---|")
     for r in rows[2:]:
         name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("gd::", "")
         alg, label = algorithmic(name, M)
         rd, wr = val(r, DRAM[0]) or 0.0, val(r, DRAM[1]) or 0.0
-        l2 = val(r, "lts__t_bytes.sum")
-        xbar = val(r, "l1tex__m_xbar2l1tex_read_bytes.sum")
+        xbar = val(r, "l1tex__m_xbar2l1tex_read_bytes.sum")       # bytes the crossbar delivered into the SMs (TMA loads,
+        l2 = xbar                                                   # generic loads, DSMEM traffic): the L2 -> SM figure
         ent = {"dram_bytes_per_launch": rd + wr, "read": rd, "write": wr, "algorithmic": alg,
-               "l2_to_sm_bytes_per_launch": l2, "xbar2l1tex_read_bytes": xbar,
+               "l2_to_sm_bytes_per_launch": l2,
+               "tma_load_bytes": val(r, "l1tex__m_xbar2l1tex_read_bytes_mem_global_op_tma_ld.sum"),
+               "dsmem_bytes": val(r, "l1tex__m_xbar2l1tex_read_bytes_mem_dshared.sum"),
+               "sm_to_l2_write_bytes": val(r, "l1tex__m_l1tex2xbar_write_bytes.sum"),
                "duration_us": val(r, "gpu__time_duration.sum"),
                "tensor_pipe_pct_active": val(r, OTHER[1]), "l2_hit_pct": val(r, "lts__t_sector_hit_rate.pct")}
         traffic[label] = ent
