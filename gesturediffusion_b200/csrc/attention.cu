@@ -296,7 +296,7 @@ extern "C" int gd_attention_f32(const float* qkv, float* out, int32_t n_seq, int
   cudaStream_t st = (cudaStream_t)stream;
 #define GD_ATF(DHV)                                                                                              \
   {                                                                                                              \
-    static size_t set = 0;                                                                                       \
+    static size_t set_dev[kMaxDevices] = {}; size_t& set = set_dev[current_device()];                                                                                       \
     if (smem > 48 * 1024 && smem > set) {                                                                        \
       GD_CUDA_OK(cudaFuncSetAttribute(attention_f32_kernel<DHV>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
                                       (int)smem));                                                               \

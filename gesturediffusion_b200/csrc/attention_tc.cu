@@ -354,7 +354,8 @@ int launch_attention_tc(const void* qkv, void* out, int n_seq, int S, int n_head
     }
     if (S >= long_min) return launch_attention_tc_long(qkv, out, n_seq, S, n_heads, fmt, stream);
   }
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device()];
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemBytes));
     attr_set = true;

@@ -319,7 +319,8 @@ attention_tc_long_kernel(const __grid_constant__ CUtensorMap tmap, const AlParam
 
 // ---------------------------------------------------------------------------- host side
 int launch_attention_tc_long(const void* qkv, void* out, int n_seq, int S, int n_heads, int fmt, cudaStream_t stream) {
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device()];
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(attention_tc_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAlSmemBytes));
     attr_set = true;

@@ -82,6 +82,15 @@ inline cudaError_t launch_pdl(int kind, void (*kernel)(KArgs...), dim3 grid, dim
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// Host-side one-off state (cudaFuncSetAttribute, scratch allocations) is per DEVICE: function attributes belong to the
+// device's context, and one process may drive several GPUs (a model on cuda:1 while cuda:0 is busy elsewhere).
+constexpr int kMaxDevices = 64;
+static inline int current_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kMaxDevices) d = 0;
+  return d;
+}
+
 // ------------------------------------------------------------------ device helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -638,7 +638,8 @@ extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t l
     }
     p.dbg = dbg;
   }
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device()];
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(ffn_ln_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFfSmemBytes));
     attr_set = true;

@@ -461,7 +461,8 @@ template <int BN, int STAGES, bool ALIAS, int MODE>
 static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p,
                           const void* res_lo, cudaStream_t stream) {
   using Cfg = LnCfg<BN, STAGES, ALIAS>;
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device()];
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));

@@ -591,7 +591,8 @@ template <int BN, int EPI>
 static int launch_gemm(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int fmt,
                        const gdEpilogue* ep, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device()];
   if (!attr_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(gemm_h16_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::kSmemBytes));

@@ -260,7 +260,8 @@ extern "C" int gd_local_attention(const float* z, const float* rope_cos, const f
       (!x_f32 || al16(x_f32)) && (!x_h16 || al16(x_h16))) {
     const size_t smem_w = ((size_t)T * LW_ES + (LW_THREADS / 32) * (2 * LW_W * LW_PS + LW_W * 2 * LW_W)) * sizeof(float);
     if (smem_w <= 200 * 1024) {
-      static size_t set_w = 0;
+      static size_t set_w_dev[kMaxDevices] = {};
+      size_t& set_w = set_w_dev[current_device()];
       if (smem_w > 48 * 1024 && smem_w > set_w) {
         GD_CUDA_OK(cudaFuncSetAttribute(local_attention_win_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)smem_w));
@@ -274,7 +275,8 @@ extern "C" int gd_local_attention(const float* z, const float* rope_cos, const f
   }
   const size_t smem = ((size_t)T * (e + 1) + (LA_THREADS / 32) * e) * sizeof(float);
   GD_REQUIRE(smem <= 200 * 1024, "gd_local_attention: T=%d too long for the shared-memory slab", T);
-  static size_t set = 0;
+  static size_t set_dev[kMaxDevices] = {};
+  size_t& set = set_dev[current_device()];
   if (smem > 48 * 1024 && smem > set) {
     GD_CUDA_OK(cudaFuncSetAttribute(local_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     set = smem;

@@ -23,7 +23,6 @@ static __device__ __align__(256) float g_noalloc_scratch[GD_NOALLOC_MAX_ELEMS];
 
 // In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol, not a device address: the address is
 // queried once per device, with that device current, and cached.
-constexpr int kMaxDevices = 64;
 static float* g_scratch_ptr[kMaxDevices] = {};
 
 static int scratch_for_current_device(float** out) {

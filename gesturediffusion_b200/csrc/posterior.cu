@@ -201,7 +201,7 @@ posterior_step_kernel(const gdPosteriorArgs a, uint32_t* block_counter) {
   }
 }
 
-static uint32_t* g_block_counter = nullptr;
+static uint32_t* g_block_counter_dev[gd::kMaxDevices] = {};        // one counter per device
 
 }  // namespace gd
 
@@ -215,14 +215,16 @@ extern "C" int gd_posterior_step(const gdPosteriorArgs* args, void* stream) {
   GD_REQUIRE(a.x_prev || a.pred_xstart || a.mean, "gd_posterior_step: no output");
   GD_REQUIRE(!a.a_next || (a.ld_a >= a.J && a.a_fmt >= GD_F32 && a.a_fmt <= GD_FP16), "gd_posterior_step: ld_a < J or bad a_fmt");
   GD_REQUIRE(a.B <= 65535, "gd_posterior_step: B too large for grid.y");
+  uint32_t*& g_block_counter = g_block_counter_dev[current_device()];
   if (a.next_t && !g_block_counter) {
-    GD_CUDA_OK(cudaMalloc(&g_block_counter, sizeof(uint32_t)));     // one-off, before any capture
+    GD_CUDA_OK(cudaMalloc(&g_block_counter, sizeof(uint32_t)));     // one-off per device, before any capture
     GD_CUDA_OK(cudaMemset(g_block_counter, 0, sizeof(uint32_t)));
   }
   const int tstride = a.T + 1 + (a.T & 1);
   const size_t smem = a.a_next ? (size_t)PS_ROWS * tstride * sizeof(float) : 0;
   GD_REQUIRE(smem <= 200 * 1024, "gd_posterior_step: T=%d too long for the transposing slab", a.T);
-  static size_t smem_set = 0;
+  static size_t smem_set_dev[kMaxDevices] = {};
+  size_t& smem_set = smem_set_dev[current_device()];
   if (smem > 48 * 1024 && smem > smem_set) {
     GD_CUDA_OK(cudaFuncSetAttribute(posterior_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_set = smem;

@@ -234,6 +234,12 @@ def cond_tokens(t, temb_table, seed_emb, pe0, x_f32, x_h16, B, n_branch, S, d, c
     _cabi.check(rc, "gd_cond_tokens")
 
 
+def on_device_of(t):
+    """Context: make `t`'s GPU the current CUDA device for the launches inside (the C ABI uses torch's current stream)."""
+    from .sampler import DeviceScope
+    return DeviceScope(t.device)
+
+
 def posterior_step(cond, x_t, coef, step_ptr, B, J, T, uncond=None, scale=None, noise=None, x_prev=None,
                    pred_xstart=None, mean=None, a_next=None, inpaint_mask=None, inpainted=None,
                    timestep_map=None, next_t=None, eps_mode=False, clip=False, const_noise=False, seed=0,
@@ -259,7 +265,7 @@ def posterior_step(cond, x_t, coef, step_ptr, B, J, T, uncond=None, scale=None, 
     a.seed, a.sample_base = seed, sample_base
     a.seed_dev = _dev(seed_dev, torch.int64, "seed_dev")
     a.ddim = int(ddim)
-    with _Timed("posterior_step", B=B, J=J, T=T, cfg=uncond is not None, philox=noise is None):
+    with _Timed("posterior_step", B=B, J=J, T=T, cfg=uncond is not None, philox=noise is None), on_device_of(x_t):
       rc = lib.gd_posterior_step(C.byref(a), _cabi.stream_handle())
     _cabi.check(rc, "gd_posterior_step")
 
@@ -276,7 +282,8 @@ def unnormalize_split(x, mean, std, pos, rot, t_off):
     lib = _cabi.load()
     B, J, T = x.shape[0], x.shape[1], x.shape[-1]
     ref = pos if pos is not None else rot
-    rc = lib.gd_unnormalize_split(_dev(x, torch.float32, "x"), _dev(mean, torch.float32, "mean") if mean is not None else None,
+    with on_device_of(x):
+      rc = lib.gd_unnormalize_split(_dev(x, torch.float32, "x"), _dev(mean, torch.float32, "mean") if mean is not None else None,
                                   _dev(std, torch.float32, "std") if std is not None else None,
                                   _dev(pos, torch.float32, "pos") if pos is not None else None,
                                   _dev(rot, torch.float32, "rot") if rot is not None else None,
@@ -286,9 +293,10 @@ def unnormalize_split(x, mean, std, pos, rot, t_off):
 
 def q_sample(x0, noise, sqrt_acp, sqrt_1macp, step, out):
     lib = _cabi.load()
-    rc = lib.gd_q_sample(_dev(x0, torch.float32, "x0"), _dev(noise, torch.float32, "noise"),
-                         _dev(sqrt_acp, torch.float32, "sqrt_acp"), _dev(sqrt_1macp, torch.float32, "sqrt_1macp"),
-                         step, _dev(out, torch.float32, "out"), x0.numel(), _cabi.stream_handle())
+    with on_device_of(x0):
+        rc = lib.gd_q_sample(_dev(x0, torch.float32, "x0"), _dev(noise, torch.float32, "noise"),
+                             _dev(sqrt_acp, torch.float32, "sqrt_acp"), _dev(sqrt_1macp, torch.float32, "sqrt_1macp"),
+                             step, _dev(out, torch.float32, "out"), x0.numel(), _cabi.stream_handle())
     _cabi.check(rc, "gd_q_sample")
 
 

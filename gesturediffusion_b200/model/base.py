@@ -126,7 +126,9 @@ class EngineBackedDenoiser(nn.Module):
                 raise K._cabi.GdError("gesturediffusion_b200 models run on CUDA only: call .to('cuda') first "
                                       "(there is no CPU fallback)")
             sd = {k: v for k, v in self.state_dict().items() if not k.startswith("clip_model.")}
-            self.__dict__["_engine"] = DenoiserEngine(sd, self._engine_cfg(), dev, self.precision)
+            from ..sampler import DeviceScope
+            with DeviceScope(dev):                          # packing launches set-up GEMMs on the model's GPU
+                self.__dict__["_engine"] = DenoiserEngine(sd, self._engine_cfg(), dev, self.precision)
             self.__dict__["_engine_sig"] = sig
         return self.__dict__["_engine"]
 
@@ -150,8 +152,9 @@ class EngineBackedDenoiser(nn.Module):
         if J * F_ != self.input_feats:
             raise ValueError("x must be [B, %d, 1, T]" % self.input_feats)
         uncond = bool(y.get('uncond', False))
-        ws = eng.workspace(B, T, 1)
-        with torch.no_grad():
+        from ..sampler import DeviceScope
+        with torch.no_grad(), DeviceScope(eng.device):
+            ws = eng.workspace(B, T, 1)
             eng.prepare_cond(ws, y, [uncond])
             eng.load_x(ws, x.to(eng.device, torch.float32).contiguous())
             ws["t"].copy_(timesteps.to(eng.device).long())

@@ -25,8 +25,9 @@ class ClassifierFreeSampleModel(nn.Module):
     def forward(self, x, timesteps, y=None):
         eng = self.model.engine()
         B, J, F_, T = x.shape
-        ws = eng.workspace(B, T, 2)
-        with torch.no_grad():
+        from ..sampler import DeviceScope
+        with torch.no_grad(), DeviceScope(eng.device):
+            ws = eng.workspace(B, T, 2)
             eng.prepare_cond(ws, y, [bool(y.get('uncond', False)), True])
             xin = x.to(eng.device, torch.float32).contiguous()
             eng.load_x(ws, xin)

@@ -22,6 +22,35 @@ STATS = {"graph_replays": 0, "graph_kernels": 0}
 MAX_GRAPHS_PER_STATE = 8
 
 
+class DeviceScope:
+    """Makes the engine's GPU the current CUDA device while kernels are launched (the C ABI takes torch's CURRENT stream,
+    and the library's one-off set-up is per current device), and restores the caller's device around every `yield` and at
+    the end -- a model on cuda:1 works while cuda:0 stays the caller's current device.  A no-op when they agree."""
+
+    def __init__(self, device):
+        self.idx = device.index if device.index is not None else torch.cuda.current_device()
+        self.prev = None
+
+    def enter(self):
+        cur = torch.cuda.current_device()
+        if cur != self.idx:
+            self.prev = cur
+            torch.cuda.set_device(self.idx)
+
+    def exit(self):
+        if self.prev is not None:
+            torch.cuda.set_device(self.prev)
+            self.prev = None
+
+    def __enter__(self):
+        self.enter()
+        return self
+
+    def __exit__(self, *exc):
+        self.exit()
+        return False
+
+
 def is_engine_model(model):
     from .model.base import EngineBackedDenoiser
     from .model.cfg_sampler import ClassifierFreeSampleModel
@@ -96,7 +125,10 @@ class FastLoop:
         if step_noise is not None and len(step_noise) < n_exec:
             raise ValueError("step_noise needs %d entries" % n_exec)
 
-        with torch.no_grad():
+        scope = DeviceScope(dev)
+        scope.enter()
+        try:
+          with torch.no_grad():
             ws = eng.workspace(B, T, nb)
             tabs = d.device_tables(dev)
             st = self._state(ws, shape, want_pred, rng != "philox", inpaint is not None)
@@ -148,7 +180,11 @@ class FastLoop:
                     self._step(ws, st, tabs, flags, coef)
                     torch.cuda.current_stream().synchronize()
                     graph = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(graph):
+                    # capture on a stream of THIS engine's GPU (torch's default capture stream is created once per process,
+                    # on whatever device was current then, and entering it would switch the current device)
+                    if getattr(eng, "_capture_stream", None) is None:
+                        eng._capture_stream = torch.cuda.Stream(device=dev)
+                    with torch.cuda.graph(graph, stream=eng._capture_stream):
                         self._step(ws, st, tabs, flags, coef)
                     st["graphs"][gkey] = (graph, coef, tabs["timestep_map"])
                     while len(st["graphs"]) > MAX_GRAPHS_PER_STATE:      # bounded: evict the least recently used
@@ -178,9 +214,13 @@ class FastLoop:
                     out = {"sample": st["x"].view(B, J, F_, T).clone()}
                     if want_pred:
                         out["pred_xstart"] = st["pred"].view(B, J, F_, T).clone()
-                    yield out
                 else:
-                    yield None
+                    out = None
+                scope.exit()                                 # the consumer runs on ITS current device
+                yield out
+                scope.enter()
+        finally:
+            scope.exit()
 
     def launches_per_step(self, rows):
         return self.engine.kernels_per_step(rows) + 1
