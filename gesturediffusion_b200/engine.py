@@ -112,6 +112,13 @@ class DenoiserEngine:
         # batches) the two GEMM kernels, which spread N over the SMs, are faster (batch 1 x 196 frames: 0.40 vs 0.50 ms per
         # denoise step; break-even near 25 row tiles, profiles/r01g_sweep.md)
         self.fuse_ffn_min_rows = int(os.environ.get("GD_FUSE_FFN_MIN_ROWS", "4096"))
+        # GEMM + residual + LayerNorm in one kernel only from this many token rows on: a 2-CTA cluster owns a whole
+        # 128-row tile, so at batch 1 (197 rows = 2 tiles) four CTAs stream the complete weight matrix (16.3 us per launch,
+        # half of the batch-1 step) where the plain GEMM spreads N over 8-16 CTAs (7 us) and gd_layernorm adds ~3 us.
+        # Measured on the batch-B no-guidance step (ms per denoise step, fused / unfused, profiles/r02r_fuse_ln_small.txt):
+        # B = 1: 0.346 / 0.293, 8: 0.387 / 0.333, 16: 0.453 / 0.403, 24 (4728 rows): 0.497 / 0.445, 32 (6304 rows):
+        # 0.541 / 0.594, 64: 0.862 / 0.960.
+        self.fuse_ln_min_rows = int(os.environ.get("GD_FUSE_LN_MIN_ROWS", "5500"))
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -322,7 +329,7 @@ class DenoiserEngine:
         xa_b = Xa if self.h16 else None
         QKV, ATT, Hh = rows("QKV"), rows("ATT"), rows("Hh")
         dh = d // self.H
-        fused_ln = self.fuse_ln and self.h16 and d in (256, 512)
+        fused_ln = self.fuse_ln and self.h16 and d in (256, 512) and (r1 - r0) >= self.fuse_ln_min_rows
         for l in range(self.L):
             p = "l%d." % l
             K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(QKV)), K=d)
@@ -360,7 +367,7 @@ class DenoiserEngine:
 
     def kernels_per_step(self, rows):
         """Kernel launches of one denoiser evaluation over `rows` token rows (nb * B * S)."""
-        per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512)) else 7
+        per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512) and rows >= self.fuse_ln_min_rows) else 7
         if (per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512
                 and self.F % 256 == 0 and rows >= self.fuse_ffn_min_rows):
             per_layer = 4

@@ -77,16 +77,25 @@ def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
     m = build_product_model(cfg, sd, cuda_device, precision)
     xd, yd, t = x.to(cuda_device), to_dev(y, cuda_device), gold["t"].to(cuda_device)
     eng = m.engine()
-    assert eng.fuse_ffn and eng.fuse_ffn_min_rows > 0       # default: fused from a few thousand token rows on
-    base = m(xd, t, yd).clone()                             # the golden cases are small: two-kernel path
-    rows = 2 * x.shape[0] * (x.shape[-1] + 1)
-    n0, min_rows = eng.kernels_per_step(rows), eng.fuse_ffn_min_rows
-    eng.fuse_ffn_min_rows = 0
+    assert eng.fuse_ffn and eng.fuse_ffn_min_rows > 0 and eng.fuse_ln_min_rows > 0   # defaults: fused from ~5 k token rows on
+    base = m(xd, t, yd).clone()                             # the golden cases are small: plain GEMM + LayerNorm kernels
+    rows = x.shape[0] * (x.shape[-1] + 1)
+    saved = (eng.fuse_ffn_min_rows, eng.fuse_ln_min_rows)
+    assert eng.kernels_per_step(rows) == 3 + (1 if cfg["arch"] == "v2" else 0) + 7 * cfg["num_layers"]
     try:
-        assert eng.kernels_per_step(rows) == n0 - cfg["num_layers"]
+        eng.fuse_ln_min_rows = 0                            # cluster GEMM+LayerNorm kernel, two-kernel feed-forward path
+        eng.fuse_ffn_min_rows = 1 << 30
+        assert eng.kernels_per_step(rows) == 3 + (1 if cfg["arch"] == "v2" else 0) + 5 * cfg["num_layers"]
+        two = m(xd, t, yd).clone()
+        eng.fuse_ffn_min_rows = 0                           # + the one-kernel feed-forward sub-layer
+        assert eng.kernels_per_step(rows) == 3 + (1 if cfg["arch"] == "v2" else 0) + 4 * cfg["num_layers"]
         fused = m(xd, t, yd).clone()
     finally:
-        eng.fuse_ffn_min_rows = min_rows
+        eng.fuse_ffn_min_rows, eng.fuse_ln_min_rows = saved
+    e_two = rel_l2(two, gold["cond"])
+    record_parity("fused ln %s %s: %.2e (vs unfused path %.2e)" % (case, precision, e_two, rel_l2(two, base)))
+    assert e_two < TOL[precision]
+    base = two
     err = rel_l2(fused, gold["cond"])
     record_parity("fused ffn %s %s: %.2e (vs two-kernel path %.2e)" % (case, precision, err, rel_l2(fused, base)))
     assert err < TOL[precision]
