@@ -379,6 +379,11 @@ def dominant_kernel_roofline(c, peaks, profile_out):
     dif_p = c.make_dif([D])
     dif_p.use_cuda_graph = False
     K.PROFILE = []
+    # Keep the GPU busy (a ~30 ms spin kernel) while the host enqueues the six eager steps and their events: otherwise the
+    # GPU outruns the host, every [start, end] event pair also spans the host's launch latency of the kernel between
+    # them, and the per-launch figure depends on the box's CPU (69.7 vs 83.0 us for the same kernel on two boxes).
+    torch.cuda.synchronize()
+    torch.cuda._sleep(int(45e6))
     dif_p.p_sample_loop(c.model, c.shape, clip_denoised=False, model_kwargs={"y": c.y_dev}, skip_timesteps=D - 6)
     summ = K.profile_summary(K.PROFILE)
     K.PROFILE = None
