@@ -20,15 +20,30 @@ sys.path.insert(0, ROOT)
 from gesturediffusion_b200 import kernels as K  # noqa: E402
 
 
+GRAPH = "--graph" in sys.argv        # time `iters` launches replayed from ONE CUDA graph: no host launch cost in the figure
+                                     # (a ~25 us kernel whose wrapper costs ~25 us of ctypes marshalling is host-bound otherwise)
+
+
 def timed(fn, iters):
     for i in range(3):
         fn(i)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(iters):
-        fn(i)
-    e1.record()
+    if GRAPH:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for i in range(iters):
+                fn(i)
+        g.replay()
+        torch.cuda.synchronize()
+        e0.record()
+        g.replay()
+        e1.record()
+    else:
+        e0.record()
+        for i in range(iters):
+            fn(i)
+        e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters * 1e3        # us
 
@@ -42,6 +57,7 @@ def main():
     ap.add_argument("--fmt", default="fp16")
     ap.add_argument("--sets", type=int, default=3)
     ap.add_argument("--only", default="")
+    ap.add_argument("--graph", action="store_true")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     act = torch.float16 if a.fmt == "fp16" else torch.bfloat16
