@@ -28,7 +28,9 @@ def main():
         K.ffn_ln_split(hi, lo, w1, b1, w2, b2, gam, bet, out_hi=oh, out_lo=ol)
     for _ in range(3):
         run()
-    buf = torch.zeros(3 * 4096, dtype=torch.int64, device=dev)
+    ws = os.environ.get("GD_FFN_WS", "0") not in ("", "0")         # ffn_ln_ws.cu: a fourth role (tail warp 4)
+    roles = ("GELU warp 0", "mma", "producer", "tail warp 4") if ws else ("epilogue warp 2", "mma", "producer")
+    buf = torch.zeros(len(roles) * 4096, dtype=torch.int64, device=dev)
     lib = _cabi.load()
     lib.gd_ffn_trace(buf.data_ptr())
     run()
@@ -36,7 +38,7 @@ def main():
     lib.gd_ffn_trace(None)
     b = buf.cpu().tolist()
     t0 = min((v & ((1 << 48) - 1)) for v in b if v)
-    for role, name in enumerate(("epilogue warp 2", "mma", "producer")):
+    for role, name in enumerate(roles):
         rec = [(v >> 48, (v & ((1 << 48) - 1)) - t0) for v in b[role * 4096:(role + 1) * 4096] if v]
         print("== %s: %d records" % (name, len(rec)))
         prev = 0
