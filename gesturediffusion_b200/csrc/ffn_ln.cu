@@ -602,12 +602,6 @@ extern "C" int gd_ffn_trace(void* buf) {
   return GD_OK;
 }
 
-namespace gd {
-int launch_ffn_ln_ws(const void* x_hi, const void* x_lo, int ld_x, const void* W1, int ldw1, const float* b1,
-                     const void* W2, int ldw2, const float* b2, int M, int N, int F, int fmt, const float* gamma,
-                     const float* beta, float eps, void* out_hi, void* out_lo, int ld_out, int dbg, cudaStream_t stream);
-}
-
 extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t ld_x, const void* W1, int32_t ldw1,
                                    const float* b1, const void* W2, int32_t ldw2, const float* b2, int32_t M,
                                    int32_t N, int32_t F, int32_t fmt, const float* gamma, const float* beta, float eps,
@@ -643,16 +637,6 @@ extern "C" int gd_ffn_h16_ln_split(const void* x_hi, const void* x_lo, int32_t l
       dbg = e ? atoi(e) : 0;
     }
     p.dbg = dbg;
-  }
-  {
-    static int ws = -1;                                      // GD_FFN_WS=1: the warp-specialised-epilogue kernel (ffn_ln_ws.cu)
-    if (ws < 0) {
-      const char* e = getenv("GD_FFN_WS");
-      ws = e ? atoi(e) : 0;
-    }
-    if (ws)
-      return launch_ffn_ln_ws(x_hi, x_lo, ld_x, W1, ldw1, b1, W2, ldw2, b2, M, N, F, fmt, gamma, beta, eps, out_hi, out_lo,
-                              ld_out, p.dbg, (cudaStream_t)stream);
   }
   static bool attr_set_dev[kMaxDevices] = {};
   bool& attr_set = attr_set_dev[current_device()];

@@ -28,8 +28,7 @@ def main():
         K.ffn_ln_split(hi, lo, w1, b1, w2, b2, gam, bet, out_hi=oh, out_lo=ol)
     for _ in range(3):
         run()
-    ws = os.environ.get("GD_FFN_WS", "0") not in ("", "0")         # ffn_ln_ws.cu: a fourth role (tail warp 4)
-    roles = ("GELU warp 0", "mma", "producer", "tail warp 4") if ws else ("epilogue warp 2", "mma", "producer")
+    roles = ("epilogue warp 2", "mma", "producer")
     buf = torch.zeros(len(roles) * 4096, dtype=torch.int64, device=dev)
     lib = _cabi.load()
     lib.gd_ffn_trace(buf.data_ptr())
