@@ -50,6 +50,29 @@ def test_gemm_bias(cuda_device, M, N, K, dtype):
     assert rel_l2(out, ref) < (2e-6 if dtype == "fp32" else 1e-5)     # fp32 accumulation in both
 
 
+@pytest.mark.parametrize("M,N,K", [(128, 512, 4980), (1, 512, 2630), (64, 512, 2630), (70, 130, 1037), (256, 512, 1024)])
+def test_gemm_f32_split_k(cuda_device, M, N, K):
+    """Few tiles, long K (the seed-pose embedding, mdm.py:186-187): a cluster of CTAs shares a tile, partial tiles are added
+    in rank order through distributed shared memory.  fp32 against float64, bit-repeatable."""
+    Kn = _K()
+    g = torch.Generator(device="cuda").manual_seed(M + 3 * K)
+    a = torch.randn(M, K, device="cuda", generator=g)
+    w = torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K)
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    ref = a.double() @ w.double().T + bias.double() + res.double()
+    outs = []
+    for _ in range(3):
+        out = torch.full((M, N), float("nan"), device="cuda")
+        Kn.gemm(a, w, Kn.epilogue(bias=bias, residual=res, out_f32=out), K=K)
+        outs.append(out)
+    torch.cuda.synchronize()
+    err = rel_l2(outs[0], ref)
+    record_parity("kernel gemm_f32 split-K M=%d N=%d K=%d: rel_l2 vs float64 %.3e" % (M, N, K, err))
+    assert err < 2e-6
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
 @pytest.mark.parametrize("M,N,K", [(700, 1024, 512), (129, 512, 64), (25216, 1024, 512)])
 @pytest.mark.parametrize("dtype", ["bf16", "fp16"])
 def test_gemm_specialised_epilogues(cuda_device, M, N, K, dtype):

@@ -136,6 +136,12 @@ def main():
     if on("ffnln"):
         rec("ffn1+gelu+ffn2+LN fused (hi,lo)", timed(lambda i: K.ffn_ln_split(Xa[i % ns], Xlo[i % ns], w_1, b_1, w_2, b_2, gam, bet, out_hi=Xa[i % ns], out_lo=Xlo[i % ns]), a.iters),
             flops=4.0 * M * d * F, nbytes=M * d * 8)
+    if on("seed"):
+        for (mb, kk) in ((128, 4980), (64, 2630), (1, 2630)):   # EmbedSeedPose: [B, 10 J] x [512, 10 J]^T, once per sampling call
+            sa, sw, sb = rnd(mb, kk), rnd(d, kk, scale=0.02), rnd(d)
+            so = torch.empty(mb, d, device=dev)
+            rec("gemm_f32 seed pose M=%d K=%d" % (mb, kk), timed(lambda i: K.gemm(sa, sw, K.epilogue(bias=sb, out_f32=so)), a.iters),
+                flops=2.0 * mb * d * kk, nbytes=4.0 * (mb * kk + d * kk + mb * d))
     if on("inproj") or on("outproj"):
         B, T, nb, J, kin = nseq // 2, S - 1, 2, 263, 296
         a_in = [rnd(B * T, kin, dtype=act) for _ in range(ns)]
