@@ -504,6 +504,12 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
 
 }  // namespace gd
 
+namespace gd {
+int launch_gemm_ln_small(const void* A, int lda, const void* W, int ldw, int M, int K, int fmt, const float* bias,
+                         const float* residual, int ld_res, const float* gamma, const float* beta, float eps,
+                         float* out_f32, int ld_out, void* out_h16, int ld_out_h16, int h16_fmt, cudaStream_t stream);
+}
+
 extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
                               int32_t fmt, const float* bias, const float* residual, int32_t ld_res,
                               const float* gamma, const float* beta, float eps, float* out_f32, int32_t ld_out,
@@ -525,6 +531,17 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
   GD_REQUIRE(ld_res >= N && ld_res % 4 == 0 && (!out_f32 || (ld_out >= N && ld_out % 4 == 0)) &&
                  (!out_h16 || (ld_out_h16 >= N && ld_out_h16 % 8 == 0)),
              "gd_gemm_h16_ln: leading dimensions must be >= N and multiples of 4 (16-bit output: 8)");
+  {
+    // few rows: an 8-CTA cluster per row tile (gemm_ln_small.cu).  GD_LN_SMALL_MAX_ROWS moves the crossover (0 = never).
+    static int small_rows = -1;
+    if (small_rows < 0) {
+      const char* e = getenv("GD_LN_SMALL_MAX_ROWS");
+      small_rows = e ? atoi(e) : 2304;
+    }
+    if (N == 512 && M <= small_rows)
+      return launch_gemm_ln_small(A, lda, W, ldw, M, K, fmt, bias, residual, ld_res, gamma, beta, eps, out_f32, ld_out,
+                                  out_h16, ld_out_h16, h16_fmt, (cudaStream_t)stream);
+  }
   LnParams p;
   p.bias = bias; p.gamma = gamma; p.beta = beta;
   p.residual = residual; p.ld_res = ld_res;

@@ -119,6 +119,8 @@ class DenoiserEngine:
         # B = 1: 0.346 / 0.293, 8: 0.387 / 0.333, 16: 0.453 / 0.403, 24 (4728 rows): 0.497 / 0.445, 32 (6304 rows):
         # 0.541 / 0.594, 64: 0.862 / 0.960.
         self.fuse_ln_min_rows = int(os.environ.get("GD_FUSE_LN_MIN_ROWS", "5500"))
+        # ... and up to this many rows the library's few-row form of the same call (one 8-CTA cluster per row tile)
+        self.fuse_ln_small_max_rows = int(os.environ.get("GD_LN_SMALL_MAX_ROWS", "2304"))
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights
@@ -330,6 +332,8 @@ class DenoiserEngine:
         QKV, ATT, Hh = rows("QKV"), rows("ATT"), rows("Hh")
         dh = d // self.H
         fused_ln = self.fuse_ln and self.h16 and d in (256, 512) and (r1 - r0) >= self.fuse_ln_min_rows
+        # few rows (batch 1-8): gd_gemm_h16_ln runs its 8-CTA-cluster kernel (gemm_ln_small.cu), fp32 residual stream
+        small_ln = self.fuse_ln and self.h16 and d == 512 and (r1 - r0) <= self.fuse_ln_small_max_rows
         for l in range(self.L):
             p = "l%d." % l
             K.gemm(Xa, w[p + "qkv.w"], K.epilogue(bias=w[p + "qkv.b"], **self._outs(QKV)), K=d)
@@ -350,7 +354,7 @@ class DenoiserEngine:
                 K.gemm_ln_split(Hh, w[p + "f2.w"], w[p + "f2.b"], w[p + "norm2.g"], w[p + "norm2.b"],
                                 out_hi=Xa, out_lo=None if last else Xlo, res_hi=Xa, res_lo=Xlo, K=self.F)
                 continue
-            if fused_ln:
+            if fused_ln or small_ln:
                 # out_proj + residual + norm1 and linear2 + residual + norm2, each in ONE kernel (2-CTA cluster
                 # LayerNorm epilogue); the residual stream X32 is updated in place
                 K.gemm_ln(ATT, w[p + "o.w"], w[p + "o.b"], X32, w[p + "norm1.g"], w[p + "norm1.b"],
@@ -368,6 +372,8 @@ class DenoiserEngine:
     def kernels_per_step(self, rows):
         """Kernel launches of one denoiser evaluation over `rows` token rows (nb * B * S)."""
         per_layer = 5 if (self.fuse_ln and self.h16 and self.d in (256, 512) and rows >= self.fuse_ln_min_rows) else 7
+        if self.fuse_ln and self.h16 and self.d == 512 and rows <= self.fuse_ln_small_max_rows:
+            per_layer = 5
         if (per_layer == 5 and self.split_residual and self.fuse_ffn and self.d == 512 and self.F >= 512
                 and self.F % 256 == 0 and rows >= self.fuse_ffn_min_rows):
             per_layer = 4

@@ -241,7 +241,10 @@ def test_layernorm(cuda_device, rows, d):
 
 
 @pytest.mark.parametrize("M,N,K", [(1, 512, 512), (127, 512, 512), (129, 256, 64), (1000, 512, 1024),
-                                   (128 * 150 + 77, 512, 512), (4100, 256, 512)])
+                                   (128 * 150 + 77, 512, 512), (4100, 256, 512),
+                                   # few rows, N = 512: the 8-CTA-cluster kernel (gemm_ln_small.cu), incl. a K tail,
+                                   # K > 8 stages, its last row count and the first one past it
+                                   (394, 512, 512), (394, 512, 1024), (300, 512, 296), (2304, 512, 512), (2305, 512, 512)])
 @pytest.mark.parametrize("dtype", ["bf16", "fp16"])
 def test_gemm_ln_fused(cuda_device, M, N, K, dtype):
     """gd_gemm_h16_ln == LayerNorm(residual + A W^T + bias) (float64 reference on the rounded operands), in place on
