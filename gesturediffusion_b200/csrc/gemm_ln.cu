@@ -58,6 +58,7 @@ struct LnParams {
   void* out_h16; int ld_out_h16; int h16_fmt;
   float eps;
   int M, K;
+  int tile_rows;   // rows per tile, in (96, 128]: the launcher balances the tiles over the clusters' rounds (see launch_gemm_ln)
   uint32_t idesc;
   int dbg;     // GD_LN_DBG diagnostics (results wrong): 1 no statistics exchange, 2 no global stores, 4 no residual, 8 no epilogue
 };
@@ -67,7 +68,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
 gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                        const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_rlo,
                        const __grid_constant__ CUtensorMap tmap_o32, const __grid_constant__ CUtensorMap tmap_o16,
+                       const __grid_constant__ CUtensorMap tmap_res_t, const __grid_constant__ CUtensorMap tmap_rlo_t,
+                       const __grid_constant__ CUtensorMap tmap_o32_t, const __grid_constant__ CUtensorMap tmap_o16_t,
                        const LnParams p) {
+  // the *_t maps are the same tensors with a box of (tile_rows - 96) rows: the fourth lane quarter of a tile shorter than
+  // 128 rows loads / stores through them, so that it never touches the next tile's rows
   // MODE 0: tmap_res fp32 residual, tmap_o32 fp32 output, tmap_o16 16-bit output (tmap_rlo unused)
   // MODE 1: tmap_res fp32 residual, tmap_o32 = lo output, tmap_o16 = hi output
   // MODE 2: tmap_res / tmap_rlo = hi / lo residual (16-bit, 64B swizzle), outputs as MODE 1
@@ -95,7 +100,8 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   const uint32_t rank = ptx::cluster_ctarank();
   const int n_clusters = (int)gridDim.x >> 1, cluster_id = (int)blockIdx.x >> 1;
   const int M = p.M;
-  const int m_tiles = (M + kLnBM - 1) / kLnBM;
+  const int tile_rows = p.tile_rows;
+  const int m_tiles = (M + tile_rows - 1) / tile_rows;
   const int k_blocks = (p.K + kLnBK - 1) / kLnBK;
   const int n_cta = (int)rank * BN;
 
@@ -106,6 +112,12 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     if constexpr (MODE == 2) ptx::prefetch_tensormap(&tmap_rlo);
     ptx::prefetch_tensormap(&tmap_o32);
     ptx::prefetch_tensormap(&tmap_o16);
+    if (tile_rows < kLnBM) {
+      ptx::prefetch_tensormap(&tmap_res_t);
+      if constexpr (MODE == 2) ptx::prefetch_tensormap(&tmap_rlo_t);
+      ptx::prefetch_tensormap(&tmap_o32_t);
+      ptx::prefetch_tensormap(&tmap_o16_t);
+    }
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < 2 * kLnEpiWarps; ++i) ptx::mbar_init(&res_bar[i], 1);
@@ -146,8 +158,9 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
           if (ptx::elect_one()) {
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-            ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kLnBK, m_blk * kLnBM);
+            // the A box has tile_rows rows; rows beyond keep stale bytes and feed accumulator lanes nobody stores
+            ptx::mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(tile_rows * kLnBK * 2 + Cfg::kBBytes));
+            ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kLnBK, m_blk * tile_rows);
             ptx::tma_load_2d(sb, &tmap_w, &full_bar[stage], kb * kLnBK, n_cta);
           }
           __syncwarp();
@@ -216,14 +229,21 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     const int n_warp = n_cta + half * CW;
     const int my_tiles = (m_tiles - cluster_id + n_clusters - 1) / n_clusters;
     const int total_blocks = my_tiles * NCH;
+    // rows of the tile in this warp's lane quarter: 32, or tile_rows - 96 in the fourth quarter of a shorter tile
+    const int rows_q = min(32, tile_rows - quarter * 32);
+    const bool tail_q = rows_q < 32;
+    const CUtensorMap* map_res = tail_q ? &tmap_res_t : &tmap_res;
+    const CUtensorMap* map_rlo = tail_q ? &tmap_rlo_t : &tmap_rlo;
+    const CUtensorMap* map_o32 = tail_q ? &tmap_o32_t : &tmap_o32;
+    const CUtensorMap* map_o16 = tail_q ? &tmap_o16_t : &tmap_o16;
     auto issue_residual = [&](int g) {                       // lane 0: residual block g of this warp's sequence
       const int tl = g / NCH, c = g - tl * NCH;
       const uint32_t bar = rbar + (uint32_t)(g & 1) * 8;
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(4096) : "memory");
-      const int row0 = (cluster_id + tl * n_clusters) * kLnBM + quarter * 32;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rows_q * 128) : "memory");
+      const int row0 = (cluster_id + tl * n_clusters) * tile_rows + quarter * 32;
       const uint32_t dst = rbuf + (uint32_t)(g & 1) * 4096;
-      ptx::tma_load_2d_s(dst, &tmap_res, bar, n_warp + c * 32, row0);           // fp32 box, or the hi box (2 KB)
-      if constexpr (MODE == 2) ptx::tma_load_2d_s(dst + 2048, &tmap_rlo, bar, n_warp + c * 32, row0);
+      ptx::tma_load_2d_s(dst, map_res, bar, n_warp + c * 32, row0);             // fp32 box, or the hi box (2 KB)
+      if constexpr (MODE == 2) ptx::tma_load_2d_s(dst + 2048, map_rlo, bar, n_warp + c * 32, row0);
     };
     if (lane == 0 && !(p.dbg & 12)) {
       if (total_blocks > 0) issue_residual(0);
@@ -234,7 +254,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
       const uint32_t par = (uint32_t)(local & 1);
-      const int m_warp = m_blk * kLnBM + quarter * 32;
+      const int m_warp = m_blk * tile_rows + quarter * 32;
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * CW);
       // this tile's statistics: 4 partials x 128 rows x 8 bytes land on stat_bar[par] of each CTA
       if (ew == 0 && lane == 0 && !(p.dbg & 8)) ptx::mbar_arrive_expect_tx(&stat_bar[par], 4 * kLnBM * 8);
@@ -430,8 +450,8 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0 && !(p.dbg & 2)) {
-          if (p.out_f32) ptx::tma_store_2d(&tmap_o32, MODE == 0 ? stg : stl, n_warp + c * 32, m_warp);
-          if (p.out_h16) ptx::tma_store_2d(&tmap_o16, MODE == 0 ? stg16 : sth, n_warp + c * 32, m_warp);
+          if (p.out_f32) ptx::tma_store_2d(map_o32, MODE == 0 ? stg : stl, n_warp + c * 32, m_warp);
+          if (p.out_h16) ptx::tma_store_2d(map_o16, MODE == 0 ? stg16 : sth, n_warp + c * 32, m_warp);
           ptx::bulk_commit();
         }
       }
@@ -458,7 +478,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 // leading dimension p.ld_out).  MODE 2: p.residual carries the hi residual and res_lo the lo residual (16-bit,
 // leading dimension p.ld_res), outputs as MODE 1.
 template <int BN, int STAGES, bool ALIAS, int MODE>
-static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p,
+static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p_in,
                           const void* res_lo, cudaStream_t stream) {
   using Cfg = LnCfg<BN, STAGES, ALIAS>;
   static bool attr_set_dev[kMaxDevices] = {};
@@ -468,36 +488,59 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
+  // Balanced row tiles.  With 128-row tiles the clusters run ceil(tiles / clusters) rounds and the last one is partly empty
+  // (25 216 rows: 197 tiles over 74 clusters = 2.66 -> 3 rounds).  The kernel is paced by the bytes of a tile, not by its
+  // MMAs, so the same number of rounds over EQUAL tiles of ceil(M / (rounds x clusters)) rows (114 here) moves fewer bytes
+  // per round.  Only when that is more than 96 rows: the fourth lane quarter then works through maps with a shorter box.
+  LnParams p = p_in;
+  const int sms = num_sms();
+  GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
+  p.tile_rows = kLnBM;
+  {
+    static int balance = -1;                                 // GD_LN_BALANCE=0: 128-row tiles always
+    if (balance < 0) {
+      const char* e = getenv("GD_LN_BALANCE");
+      balance = e ? atoi(e) : 1;
+    }
+    const int t128 = ceil_div(p.M, kLnBM), cl = t128 < sms / 2 ? t128 : sms / 2;
+    const int rounds = ceil_div(t128, cl);
+    const int even = ceil_div(p.M, rounds * cl);
+    if (balance && rounds >= 2 && even > 96 && even < kLnBM) p.tile_rows = even;
+  }
+  const int tail_rows = p.tile_rows < kLnBM ? p.tile_rows - 96 : 32;
   CUtensorMap ta, tw;
-  int rc = make_tmap_2d(&ta, A, p.M, p.K, lda, kLnBM, fmt);
+  int rc = make_tmap_2d(&ta, A, p.M, p.K, lda, p.tile_rows, fmt);
   if (rc) return rc;
   rc = make_tmap_2d(&tw, W, 2 * BN, p.K, ldw, BN, fmt);
   if (rc) return rc;
-  CUtensorMap tr;
-  if (MODE == 2) rc = make_tmap_2d_h16_sw64(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32, p.h16_fmt);
-  else rc = make_tmap_2d_f32(&tr, p.residual, p.M, 2 * BN, p.ld_res, 32);
-  if (rc) return rc;
-  CUtensorMap trlo = tr;
-  if (MODE == 2) {
-    rc = make_tmap_2d_h16_sw64(&trlo, res_lo, p.M, 2 * BN, p.ld_res, 32, p.h16_fmt);
+  CUtensorMap tr[2], trlo[2], to32[2], to16[2];              // [0] 32-row boxes, [1] tail_rows-row boxes
+  for (int t = 0; t < 2; ++t) {
+    const int br = t == 0 ? 32 : tail_rows;
+    if (MODE == 2) rc = make_tmap_2d_h16_sw64(&tr[t], p.residual, p.M, 2 * BN, p.ld_res, br, p.h16_fmt);
+    else rc = make_tmap_2d_f32(&tr[t], p.residual, p.M, 2 * BN, p.ld_res, br);
     if (rc) return rc;
+    trlo[t] = tr[t];
+    if (MODE == 2) {
+      rc = make_tmap_2d_h16_sw64(&trlo[t], res_lo, p.M, 2 * BN, p.ld_res, br, p.h16_fmt);
+      if (rc) return rc;
+    }
+    to32[t] = tr[t];                                         // placeholders when an output is absent (never used)
+    to16[t] = tr[t];
+    if (p.out_f32) {
+      if (MODE == 0) rc = make_tmap_2d_f32(&to32[t], p.out_f32, p.M, 2 * BN, p.ld_out, br);
+      else rc = make_tmap_2d_h16_sw64(&to32[t], p.out_f32, p.M, 2 * BN, p.ld_out, br, p.h16_fmt);
+      if (rc) return rc;
+    }
+    if (p.out_h16) {
+      rc = make_tmap_2d_h16_sw64(&to16[t], p.out_h16, p.M, 2 * BN, p.ld_out_h16, br, p.h16_fmt);
+      if (rc) return rc;
+    }
   }
-  CUtensorMap to32 = tr, to16 = tr;                          // placeholders when an output is absent (never used)
-  if (p.out_f32) {
-    if (MODE == 0) rc = make_tmap_2d_f32(&to32, p.out_f32, p.M, 2 * BN, p.ld_out, 32);
-    else rc = make_tmap_2d_h16_sw64(&to32, p.out_f32, p.M, 2 * BN, p.ld_out, 32, p.h16_fmt);
-    if (rc) return rc;
-  }
-  if (p.out_h16) {
-    rc = make_tmap_2d_h16_sw64(&to16, p.out_h16, p.M, 2 * BN, p.ld_out_h16, 32, p.h16_fmt);
-    if (rc) return rc;
-  }
-  const int sms = num_sms();
-  GD_REQUIRE(sms >= 2, "gd_gemm_h16_ln: cannot query the SM count");
-  const int m_tiles = ceil_div(p.M, kLnBM);
+  const int m_tiles = ceil_div(p.M, p.tile_rows);
   const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
   GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE>, dim3(2 * clusters),
-                        dim3(kLnThreads), Cfg::kSmemBytes, stream, ta, tw, tr, trlo, to32, to16, p));
+                        dim3(kLnThreads), Cfg::kSmemBytes, stream, ta, tw, tr[0], trlo[0], to32[0], to16[0], tr[1], trlo[1],
+                        to32[1], to16[1], p));
   GD_LAUNCH_CHECK();
   return GD_OK;
 }

@@ -244,7 +244,9 @@ def test_layernorm(cuda_device, rows, d):
                                    (128 * 150 + 77, 512, 512), (4100, 256, 512),
                                    # few rows, N = 512: the 8-CTA-cluster kernel (gemm_ln_small.cu), incl. a K tail,
                                    # K > 8 stages, its last row count and the first one past it
-                                   (394, 512, 512), (394, 512, 1024), (300, 512, 296), (2304, 512, 512), (2305, 512, 512)])
+                                   (394, 512, 512), (394, 512, 1024), (300, 512, 296), (2304, 512, 512), (2305, 512, 512),
+                                   # balanced row tiles (110 / 105 / 122 rows instead of 128: fourth-quarter tail boxes)
+                                   (24325, 512, 512), (30976, 512, 1024), (17923, 512, 512), (17923, 256, 512)])
 @pytest.mark.parametrize("dtype", ["bf16", "fp16"])
 def test_gemm_ln_fused(cuda_device, M, N, K, dtype):
     """gd_gemm_h16_ln == LayerNorm(residual + A W^T + bias) (float64 reference on the rounded operands), in place on
@@ -305,7 +307,8 @@ def test_gemm_ln_repeatable_under_load(cuda_device):
 
 
 @pytest.mark.parametrize("M,N,K", [(1, 512, 512), (127, 512, 512), (129, 256, 64), (1000, 512, 1024),
-                                   (128 * 150 + 77, 512, 512), (25216, 512, 1024)])
+                                   (128 * 150 + 77, 512, 512), (25216, 512, 1024),
+                                   (24325, 512, 512), (30976, 512, 512), (17923, 256, 512)])   # balanced row tiles
 @pytest.mark.parametrize("dtype", ["bf16", "fp16"])
 def test_gemm_ln_split_residual(cuda_device, M, N, K, dtype):
     """gd_gemm_h16_ln_split: the residual stream as a 16-bit (hi, lo) pair.  fp32 residual in -> pair out equals the
@@ -325,8 +328,13 @@ def test_gemm_ln_split_residual(cuda_device, M, N, K, dtype):
     hi = torch.zeros(M, N, device="cuda", dtype=tdt)
     lo = torch.full((M, N), 7.0, device="cuda", dtype=tdt)
     Kn.gemm_ln_split(a, w, bias, gamma, beta, out_hi=hi, out_lo=lo, res_f32=res)
-    assert torch.equal(hi, x32.to(tdt))
-    assert torch.equal(lo, (x32 - hi.float()).to(tdt))
+    if N == 512 and M <= 2304:
+        # few rows: gd_gemm_h16_ln runs its 8-CTA-cluster kernel (other order of the fp32 sums), the split form the 2-CTA
+        # one -- equal up to an fp32 rounding step, i.e. a different 16-bit value in rare elements
+        assert (hi != x32.to(tdt)).float().mean() < 2e-3
+    else:
+        assert torch.equal(hi, x32.to(tdt))
+        assert torch.equal(lo, (x32 - hi.float()).to(tdt))
     recon = hi.float() + lo.float()
     assert rel_l2(recon, x32) < (3e-7 if dtype == "fp16" else 2e-5)
     # pair in, in place, pair out: the next sub-layer
