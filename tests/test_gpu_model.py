@@ -78,11 +78,21 @@ def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
     xd, yd, t = x.to(cuda_device), to_dev(y, cuda_device), gold["t"].to(cuda_device)
     eng = m.engine()
     assert eng.fuse_ffn and eng.fuse_ffn_min_rows > 0 and eng.fuse_ln_min_rows > 0   # defaults: fused from ~5 k token rows on
-    base = m(xd, t, yd).clone()                             # the golden cases are small: plain GEMM + LayerNorm kernels
     rows = x.shape[0] * (x.shape[-1] + 1)
-    saved = (eng.fuse_ffn_min_rows, eng.fuse_ln_min_rows)
-    assert eng.kernels_per_step(rows) == 3 + (1 if cfg["arch"] == "v2" else 0) + 7 * cfg["num_layers"]
+    front = 3 + (1 if cfg["arch"] == "v2" else 0)
+    saved = (eng.fuse_ffn_min_rows, eng.fuse_ln_min_rows, eng.fuse_ln_small_max_rows)
+    # the golden cases are small: at d = 512 the few-row GEMM + LayerNorm kernel (8-CTA cluster per row tile) ...
+    assert eng.fuse_ln_small_max_rows >= rows
+    assert eng.kernels_per_step(rows) == front + (5 if eng.d == 512 else 7) * cfg["num_layers"]
+    small = m(xd, t, yd).clone()
     try:
+        eng.fuse_ln_small_max_rows = 0                      # ... otherwise plain GEMM + LayerNorm kernels
+        assert eng.kernels_per_step(rows) == front + 7 * cfg["num_layers"]
+        base = m(xd, t, yd).clone()
+        e_small = rel_l2(small, gold["cond"])
+        record_parity("few-row ln %s %s: %.2e (vs unfused path %.2e)" % (case, precision, e_small, rel_l2(small, base)))
+        assert e_small < TOL[precision]
+        assert rel_l2(small, base) < TOL[precision]
         eng.fuse_ln_min_rows = 0                            # cluster GEMM+LayerNorm kernel, two-kernel feed-forward path
         eng.fuse_ffn_min_rows = 1 << 30
         assert eng.kernels_per_step(rows) == 3 + (1 if cfg["arch"] == "v2" else 0) + 5 * cfg["num_layers"]
@@ -91,7 +101,7 @@ def test_forward_with_fused_ffn_kernel(cuda_device, case, precision):
         assert eng.kernels_per_step(rows) == 3 + (1 if cfg["arch"] == "v2" else 0) + 4 * cfg["num_layers"]
         fused = m(xd, t, yd).clone()
     finally:
-        eng.fuse_ffn_min_rows, eng.fuse_ln_min_rows = saved
+        eng.fuse_ffn_min_rows, eng.fuse_ln_min_rows, eng.fuse_ln_small_max_rows = saved
     e_two = rel_l2(two, gold["cond"])
     record_parity("fused ln %s %s: %.2e (vs unfused path %.2e)" % (case, precision, e_two, rel_l2(two, base)))
     assert e_two < TOL[precision]
