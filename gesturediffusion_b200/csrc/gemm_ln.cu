@@ -36,7 +36,7 @@ constexpr int kLnBM = 128, kLnBK = 64, kLnEpiWarps = 8, kLnThreads = 320;
 // ALIAS = false: per epilogue warp two residual blocks in flight (also across tile boundaries) plus separate
 // staging blocks.  ALIAS = true (one more operand stage for long K, main loop bound by the operand bytes in flight): the staging blocks alias the
 // two residual blocks, so the first residual blocks of a tile are only requested when the previous tile has left.
-template <int BN, int STAGES, bool ALIAS>
+template <int BN, int STAGES, bool ALIAS, int CL = 2>
 struct LnCfg {
   static constexpr bool kAlias = ALIAS;
   static constexpr int kWarpRing = kAlias ? 2 * 4096 : 3 * 4096 + 2048;
@@ -45,7 +45,8 @@ struct LnCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kRingBytes = kLnEpiWarps * kWarpRing;
   static constexpr int kVecBytes = 3 * BN * 4;                  // bias, gamma, beta slices of this CTA
-  static constexpr int kStatBytes = 2 * 4 * kLnBM * 8;          // [parity][part][row] (mean, M2)
+  static constexpr int kParts = 2 * CL;                         // partial statistics per row: 2 column halves x CL CTAs
+  static constexpr int kStatBytes = 2 * kParts * kLnBM * 8;     // [parity][part][row] (mean, M2)
   static constexpr int kBarBytes = 512;
   static constexpr int kSmemBytes = STAGES * kStageBytes + kRingBytes + kVecBytes + kStatBytes + kBarBytes;
   static constexpr int kTmemCols = 2 * BN;
@@ -63,8 +64,8 @@ struct LnParams {
   int dbg;     // GD_LN_DBG diagnostics (results wrong): 1 no statistics exchange, 2 no global stores, 4 no residual, 8 no epilogue
 };
 
-template <int BN, int STAGES, bool ALIAS, int MODE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kLnThreads, 1)
+template <int BN, int STAGES, bool ALIAS, int MODE, int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(kLnThreads, 1)
 gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                        const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_rlo,
                        const __grid_constant__ CUtensorMap tmap_o32, const __grid_constant__ CUtensorMap tmap_o16,
@@ -76,10 +77,11 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   // MODE 0: tmap_res fp32 residual, tmap_o32 fp32 output, tmap_o16 16-bit output (tmap_rlo unused)
   // MODE 1: tmap_res fp32 residual, tmap_o32 = lo output, tmap_o16 = hi output
   // MODE 2: tmap_res / tmap_rlo = hi / lo residual (16-bit, 64B swizzle), outputs as MODE 1
-  using Cfg = LnCfg<BN, STAGES, ALIAS>;
+  using Cfg = LnCfg<BN, STAGES, ALIAS, CL>;
   constexpr int kLnStages = STAGES;
   constexpr bool kAlias = Cfg::kAlias;
-  constexpr int N = 2 * BN;
+  constexpr int N = CL * BN;
+  constexpr uint32_t P = (uint32_t)Cfg::kParts;
   extern __shared__ __align__(1024) uint8_t smem[];
   if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* ring = smem + kLnStages * Cfg::kStageBytes;
@@ -98,7 +100,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   // descriptor arithmetic runs in the uniform datapath (no ELECT / R2UR waterfall around every UTCHMMA)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
-  const int n_clusters = (int)gridDim.x >> 1, cluster_id = (int)blockIdx.x >> 1;
+  const int n_clusters = (int)gridDim.x / CL, cluster_id = (int)blockIdx.x / CL;
   const int M = p.M;
   const int tile_rows = p.tile_rows;
   const int m_tiles = (M + tile_rows - 1) / tile_rows;
@@ -221,9 +223,13 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     const uint32_t rbar = ptx::smem_u32(&res_bar[2 * ew]);
     const uint32_t vec_s = ptx::smem_u32(vecs) + (uint32_t)(half * CW) * 4;      // this warp's bias slice
     const uint32_t stats_s = ptx::smem_u32(stats);
-    const uint32_t stats_cl[2] = {ptx::mapa(stats_s, rank), ptx::mapa(stats_s, rank ^ 1u)};
+    uint32_t stats_cl[CL], sbar_cl[CL];
     const uint32_t sbar_s = ptx::smem_u32(stat_bar);
-    const uint32_t sbar_cl[2] = {ptx::mapa(sbar_s, rank), ptx::mapa(sbar_s, rank ^ 1u)};
+#pragma unroll
+    for (int r = 0; r < CL; ++r) {
+      stats_cl[r] = ptx::mapa(stats_s, (uint32_t)r);
+      sbar_cl[r] = ptx::mapa(sbar_s, (uint32_t)r);
+    }
     const uint32_t part = rank * 2u + (uint32_t)half;
     const int row_in_tile = quarter * 32 + lane;
     const int n_warp = n_cta + half * CW;
@@ -257,7 +263,7 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       const int m_warp = m_blk * tile_rows + quarter * 32;
       const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * CW);
       // this tile's statistics: 4 partials x 128 rows x 8 bytes land on stat_bar[par] of each CTA
-      if (ew == 0 && lane == 0 && !(p.dbg & 8)) ptx::mbar_arrive_expect_tx(&stat_bar[par], 4 * kLnBM * 8);
+      if (ew == 0 && lane == 0 && !(p.dbg & 8)) ptx::mbar_arrive_expect_tx(&stat_bar[par], P * kLnBM * 8);
       ptx::mbar_wait(&tfull_bar[buf], use & 1);
       ptx::tc_fence_after();
       if (p.dbg & 8) {
@@ -358,23 +364,23 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       // ---- exchange: every thread sends its row's partial (mean, M2) to both CTAs of the cluster; the store
       // itself completes transaction bytes on the destination's barrier (no fence, no separate arrive)
       {
-        const uint32_t off = ((par * 4u + part) * kLnBM + (uint32_t)row_in_tile) * 8u;
-        ptx::st_async_v2(stats_cl[0] + off, r_mean, r_m2, sbar_cl[0] + par * 8u);
-        ptx::st_async_v2(stats_cl[1] + off, r_mean, r_m2, sbar_cl[1] + par * 8u);
+        const uint32_t off = ((par * P + part) * kLnBM + (uint32_t)row_in_tile) * 8u;
+#pragma unroll
+        for (int r = 0; r < CL; ++r) ptx::st_async_v2(stats_cl[r] + off, r_mean, r_m2, sbar_cl[r] + par * 8u);
       }
       if (!(p.dbg & 1)) ptx::mbar_wait(&stat_bar[par], use & 1);
       float mean = 0.f, m2 = 0.f;
       {
-        float pm[4], pq[4];
+        float pm[P], pq[P];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t a = stats_s + ((par * 4u + (uint32_t)q) * kLnBM + (uint32_t)row_in_tile) * 8u;
+        for (uint32_t q = 0; q < P; ++q) {
+          const uint32_t a = stats_s + ((par * P + q) * kLnBM + (uint32_t)row_in_tile) * 8u;
           asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(pm[q]), "=f"(pq[q]) : "r"(a) : "memory");
           mean += pm[q];
         }
-        mean *= 0.25f;
+        mean *= 1.0f / (float)P;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) m2 += pq[q] + (float)CW * (pm[q] - mean) * (pm[q] - mean);
+        for (uint32_t q = 0; q < P; ++q) m2 += pq[q] + (float)CW * (pm[q] - mean) * (pm[q] - mean);
       }
       const float rstd = rsqrtf(m2 * (1.0f / (float)N) + p.eps);
       const float shift = -mean * rstd;
@@ -477,15 +483,37 @@ gemm_ln_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 // MODE 0: p.residual / p.out_f32 are fp32.  MODE 1: p.residual fp32, p.out_f32 carries the lo output (16-bit,
 // leading dimension p.ld_out).  MODE 2: p.residual carries the hi residual and res_lo the lo residual (16-bit,
 // leading dimension p.ld_res), outputs as MODE 1.
-template <int BN, int STAGES, bool ALIAS, int MODE>
+template <int BN, int STAGES, bool ALIAS, int MODE, int CL = 2>
 static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fmt, const LnParams& p_in,
                           const void* res_lo, cudaStream_t stream) {
-  using Cfg = LnCfg<BN, STAGES, ALIAS>;
+  using Cfg = LnCfg<BN, STAGES, ALIAS, CL>;
+  static_assert(Cfg::kSmemBytes <= 232448, "shared memory");
   static bool attr_set_dev[kMaxDevices] = {};
+  static int max_clusters_dev[kMaxDevices] = {};
   bool& attr_set = attr_set_dev[current_device()];
+  int& max_clusters = max_clusters_dev[current_device()];
   if (!attr_set) {
-    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE>,
+    GD_CUDA_OK(cudaFuncSetAttribute(gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE, CL>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    max_clusters = num_sms() / CL;
+    if (CL > 2) {                                            // clusters that fit the GPCs at once (a GPC of 18 SMs holds 4 of 4)
+      cudaLaunchConfig_t qc = {};
+      qc.gridDim = dim3(CL * (num_sms() / CL));
+      qc.blockDim = dim3(kLnThreads);
+      qc.dynamicSmemBytes = Cfg::kSmemBytes;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = CL;
+      qa[0].val.clusterDim.y = 1;
+      qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa;
+      qc.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE, CL>, &qc) == cudaSuccess && n > 0)
+        max_clusters = n < max_clusters ? n : max_clusters;
+      else
+        (void)cudaGetLastError();
+    }
     attr_set = true;
   }
   // Balanced row tiles.  With 128-row tiles the clusters run ceil(tiles / clusters) rounds and the last one is partly empty
@@ -502,7 +530,7 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
       const char* e = getenv("GD_LN_BALANCE");
       balance = e ? atoi(e) : 1;
     }
-    const int t128 = ceil_div(p.M, kLnBM), cl = t128 < sms / 2 ? t128 : sms / 2;
+    const int t128 = ceil_div(p.M, kLnBM), cl = t128 < max_clusters ? t128 : max_clusters;
     const int rounds = ceil_div(t128, cl);
     const int even = ceil_div(p.M, rounds * cl);
     if (balance && rounds >= 2 && even > 96 && even < kLnBM) p.tile_rows = even;
@@ -511,34 +539,34 @@ static int launch_gemm_ln(const void* A, int lda, const void* W, int ldw, int fm
   CUtensorMap ta, tw;
   int rc = make_tmap_2d(&ta, A, p.M, p.K, lda, p.tile_rows, fmt);
   if (rc) return rc;
-  rc = make_tmap_2d(&tw, W, 2 * BN, p.K, ldw, BN, fmt);
+  rc = make_tmap_2d(&tw, W, CL * BN, p.K, ldw, BN, fmt);
   if (rc) return rc;
   CUtensorMap tr[2], trlo[2], to32[2], to16[2];              // [0] 32-row boxes, [1] tail_rows-row boxes
   for (int t = 0; t < 2; ++t) {
     const int br = t == 0 ? 32 : tail_rows;
-    if (MODE == 2) rc = make_tmap_2d_h16_sw64(&tr[t], p.residual, p.M, 2 * BN, p.ld_res, br, p.h16_fmt);
-    else rc = make_tmap_2d_f32(&tr[t], p.residual, p.M, 2 * BN, p.ld_res, br);
+    if (MODE == 2) rc = make_tmap_2d_h16_sw64(&tr[t], p.residual, p.M, CL * BN, p.ld_res, br, p.h16_fmt);
+    else rc = make_tmap_2d_f32(&tr[t], p.residual, p.M, CL * BN, p.ld_res, br);
     if (rc) return rc;
     trlo[t] = tr[t];
     if (MODE == 2) {
-      rc = make_tmap_2d_h16_sw64(&trlo[t], res_lo, p.M, 2 * BN, p.ld_res, br, p.h16_fmt);
+      rc = make_tmap_2d_h16_sw64(&trlo[t], res_lo, p.M, CL * BN, p.ld_res, br, p.h16_fmt);
       if (rc) return rc;
     }
     to32[t] = tr[t];                                         // placeholders when an output is absent (never used)
     to16[t] = tr[t];
     if (p.out_f32) {
-      if (MODE == 0) rc = make_tmap_2d_f32(&to32[t], p.out_f32, p.M, 2 * BN, p.ld_out, br);
-      else rc = make_tmap_2d_h16_sw64(&to32[t], p.out_f32, p.M, 2 * BN, p.ld_out, br, p.h16_fmt);
+      if (MODE == 0) rc = make_tmap_2d_f32(&to32[t], p.out_f32, p.M, CL * BN, p.ld_out, br);
+      else rc = make_tmap_2d_h16_sw64(&to32[t], p.out_f32, p.M, CL * BN, p.ld_out, br, p.h16_fmt);
       if (rc) return rc;
     }
     if (p.out_h16) {
-      rc = make_tmap_2d_h16_sw64(&to16[t], p.out_h16, p.M, 2 * BN, p.ld_out_h16, br, p.h16_fmt);
+      rc = make_tmap_2d_h16_sw64(&to16[t], p.out_h16, p.M, CL * BN, p.ld_out_h16, br, p.h16_fmt);
       if (rc) return rc;
     }
   }
   const int m_tiles = ceil_div(p.M, p.tile_rows);
-  const int clusters = m_tiles < sms / 2 ? m_tiles : sms / 2;
-  GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE>, dim3(2 * clusters),
+  const int clusters = m_tiles < max_clusters ? m_tiles : max_clusters;
+  GD_CUDA_OK(launch_pdl(PDL_GEMM_LN, gemm_ln_tcgen05_kernel<BN, STAGES, ALIAS, MODE, CL>, dim3(CL * clusters),
                         dim3(kLnThreads), Cfg::kSmemBytes, stream, ta, tw, tr[0], trlo[0], to32[0], to16[0], tr[1], trlo[1],
                         to32[1], to16[1], p));
   GD_LAUNCH_CHECK();
@@ -658,6 +686,16 @@ extern "C" int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, i
   if (shallow_k < 0) {
     const char* e = getenv("GD_LN_SHALLOW_K");
     shallow_k = e ? atoi(e) : 0;
+  }
+  static int cl4 = -1;                                       // GD_LN_CL=4: four CTAs of 128 columns per row tile (N = 512)
+  if (cl4 < 0) {
+    const char* e = getenv("GD_LN_CL");
+    cl4 = (e && atoi(e) == 4) ? 1 : 0;
+  }
+  if (N == 512 && cl4) {
+    p.idesc = ptx::umma_idesc_h16_f32(kLnBM, 128, fmt == GD_FP16);
+    return split_in ? launch_gemm_ln<128, 4, true, 2, 4>(A, lda, W, ldw, fmt, p, res_lo, st)
+                    : launch_gemm_ln<128, 4, true, 1, 4>(A, lda, W, ldw, fmt, p, nullptr, st);
   }
   if (N == 512 && K <= shallow_k)
     return split_in ? launch_gemm_ln<256, 2, false, 2>(A, lda, W, ldw, fmt, p, res_lo, st)
