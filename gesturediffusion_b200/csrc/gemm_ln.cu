@@ -687,16 +687,6 @@ extern "C" int gd_gemm_h16_ln_split(const void* A, int32_t lda, const void* W, i
     const char* e = getenv("GD_LN_SHALLOW_K");
     shallow_k = e ? atoi(e) : 0;
   }
-  static int cl4 = -1;                                       // GD_LN_CL=4: four CTAs of 128 columns per row tile (N = 512)
-  if (cl4 < 0) {
-    const char* e = getenv("GD_LN_CL");
-    cl4 = (e && atoi(e) == 4) ? 1 : 0;
-  }
-  if (N == 512 && cl4) {
-    p.idesc = ptx::umma_idesc_h16_f32(kLnBM, 128, fmt == GD_FP16);
-    return split_in ? launch_gemm_ln<128, 4, true, 2, 4>(A, lda, W, ldw, fmt, p, res_lo, st)
-                    : launch_gemm_ln<128, 4, true, 1, 4>(A, lda, W, ldw, fmt, p, nullptr, st);
-  }
   if (N == 512 && K <= shallow_k)
     return split_in ? launch_gemm_ln<256, 2, false, 2>(A, lda, W, ldw, fmt, p, res_lo, st)
                     : launch_gemm_ln<256, 2, false, 1>(A, lda, W, ldw, fmt, p, nullptr, st);
