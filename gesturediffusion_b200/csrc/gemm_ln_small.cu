@@ -65,7 +65,10 @@ gemm_ln_small_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const _
   if (warp == 1) ptx::tmem_alloc(tmem_slot, 64);
   ptx::tc_fence_before();
   __syncthreads();
-  ptx::cluster_sync_all();                                   // every CTA's stat_bar is armed before a peer's st.async lands
+  // Every CTA's stat_bar must be armed before a peer's st.async lands: all threads ARRIVE on the cluster barrier here and
+  // WAIT where they need it -- the epilogue warps just before their first remote store, i.e. after the main loop, so the
+  // cluster-wide rendezvous costs nothing on the way to the first TMA load.
+  ptx::cluster_arrive();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   ptx::grid_dep_wait();                                      // prologue above overlaps the previous kernel's tail
@@ -85,6 +88,8 @@ gemm_ln_small_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const _
         if (++stage == kSmStages) { stage = 0; phase ^= 1; }
       }
     }
+    __syncwarp();
+    ptx::cluster_wait();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ UMMA issuer (whole warp, one elected lane)
     int stage = 0;
@@ -108,6 +113,7 @@ gemm_ln_small_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const _
     }
     if (ptx::elect_one()) ptx::umma_commit(tfull_bar);
     __syncwarp();
+    ptx::cluster_wait();
   } else {
     // ------------------------------------------------------------------ epilogue: warps 2..5, one row per thread
     const int quarter = warp & 3;                            // the TMEM lane quarter this warp may access
@@ -169,6 +175,7 @@ gemm_ln_small_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const _
     const uint32_t stats_s = ptx::smem_u32(smem + kSmStatOff);
     const uint32_t sbar_s = ptx::smem_u32(stat_bar);
     const uint32_t off = (rank * kSmBM + (uint32_t)row) * 8u;
+    ptx::cluster_wait();                                     // the peers' barriers are armed (arrive: kernel prologue)
 #pragma unroll
     for (uint32_t r = 0; r < (uint32_t)kSmCluster; ++r)
       ptx::st_async_v2(ptx::mapa(stats_s, r) + off, pmean, pm2, ptx::mapa(sbar_s, r));
@@ -218,9 +225,10 @@ gemm_ln_small_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const _
     }
   }
 
+  // No cluster barrier at the end: the only remote accesses are the st.async pushes, and a CTA has waited for all eight
+  // partials to land in its own shared memory before it gets here; its own pushes carry their data with them.
   ptx::tc_fence_before();
   __syncthreads();
-  ptx::cluster_sync_all();                                   // no CTA exits while a peer's partials may still be landing
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 64);
