@@ -98,141 +98,12 @@ local_attention_kernel(const float* __restrict__ z, const float* __restrict__ rc
   }
 }
 
-// Fast path for the reference's configuration (head dim 64, window 10): one warp per WINDOW instead of per row.
-// The 10 queries of window w share their 20 candidate keys (window w-1 and w), so
-//   scores: lane = key; each key row is read once per 4 channels (LDS.128, row stride E+4 -> conflict-free) and
-//           the 10 query rows arrive as warp-uniform LDS.128 broadcasts: 40 FMA per 11 shared-memory loads;
-//   softmax: scores go to a [10][20] per-warp scratch, lane q < 10 normalises query q; P goes to a [20][12] scratch;
-//   P V:    lane = channel pair; per key one LDS.64 of V and three broadcast loads of its 10 probabilities;
-//   second RoPE at position t+1 through a lane^16 shuffle (channel pair i, i+32), 256 B fp32 + 128 B 16-bit
-//           row stores straight into rows 1..T of the encoder input.
-constexpr int LW_THREADS = 192, LW_E = 64, LW_ES = LW_E + 4, LW_W = 10, LW_PS = 12;
-
-__global__ void __launch_bounds__(LW_THREADS)
-local_attention_win_kernel(const float* __restrict__ z, const float* __restrict__ rcos, const float* __restrict__ rsin,
-                           float* __restrict__ x_f32, uint16_t* __restrict__ x_h16, int h16_fmt, int T, int d,
-                           float scale) {
-  extern __shared__ __align__(16) float sm[];
-  float* slab = sm;                                   // [T][LW_ES] rotated q = k = v
-  float* pscr = sm + (size_t)T * LW_ES;               // [warps]: P [2*LW_W][LW_PS] + S [LW_W][2*LW_W]
-  const int head = blockIdx.x, seq = blockIdx.y;
-  constexpr int E = LW_E, HALF = E / 2;
-  const float* zs = z + (size_t)seq * T * d + head * E;
-  for (int idx = threadIdx.x; idx < T * (E / 4); idx += LW_THREADS) {
-    const int t = idx / (E / 4), i = (idx - t * (E / 4)) * 4;
-    const float4 x = *reinterpret_cast<const float4*>(zs + (size_t)t * d + i);
-    const float4 pr = *reinterpret_cast<const float4*>(zs + (size_t)t * d + (i ^ HALF));
-    const float4 c = __ldg(reinterpret_cast<const float4*>(rcos + t * E + i));
-    const float4 sn = __ldg(reinterpret_cast<const float4*>(rsin + t * E + i));
-    const float sg = (i < HALF) ? -1.f : 1.f;
-    float4 o;
-    o.x = x.x * c.x + sg * pr.x * sn.x;
-    o.y = x.y * c.y + sg * pr.y * sn.y;
-    o.z = x.z * c.z + sg * pr.z * sn.z;
-    o.w = x.w * c.w + sg * pr.w * sn.w;
-    *reinterpret_cast<float4*>(slab + t * LW_ES + i) = o;
-  }
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* P = pscr + warp * (2 * LW_W * LW_PS + LW_W * 2 * LW_W);
-  const int S = T + 1, n_win = T / LW_W;
-  for (int w = warp; w < n_win; w += LW_THREADS / 32) {
-    const int t0 = w * LW_W, kbeg = t0 - LW_W;
-    // ---- scores of the 10 queries against key `lane` (lanes >= 20 and the missing look-back of window 0 idle)
-    const bool key_live = lane < 2 * LW_W && (w > 0 || lane >= LW_W);
-    const float* kr = slab + (key_live ? kbeg + lane : t0) * LW_ES;
-    const float* q0 = slab + t0 * LW_ES;
-    float acc[LW_W];
-#pragma unroll
-    for (int q = 0; q < LW_W; ++q) acc[q] = 0.f;
-#pragma unroll 4
-    for (int i = 0; i < E; i += 4) {
-      const float4 k4 = *reinterpret_cast<const float4*>(kr + i);
-#pragma unroll
-      for (int q = 0; q < LW_W; ++q) {
-        const float4 q4 = *reinterpret_cast<const float4*>(q0 + q * LW_ES + i);
-        acc[q] = fmaf(q4.x, k4.x, acc[q]);
-        acc[q] = fmaf(q4.y, k4.y, acc[q]);
-        acc[q] = fmaf(q4.z, k4.z, acc[q]);
-        acc[q] = fmaf(q4.w, k4.w, acc[q]);
-      }
-    }
-    // ---- causal window softmax: scores -> S[query][key] scratch; lane q < 10 owns query q (sequential over its 20
-    // keys: ~10x fewer issue slots than ten shuffle reductions); normalised probabilities -> P[key][query]
-    float* Sc = P + 2 * LW_W * LW_PS;                   // [LW_W][2*LW_W]
-    if (lane < 2 * LW_W) {
-#pragma unroll
-      for (int q = 0; q < LW_W; ++q) Sc[q * (2 * LW_W) + lane] = acc[q] * scale;
-    }
-    __syncwarp();
-    if (lane < LW_W) {
-      float sc[2 * LW_W];
-#pragma unroll
-      for (int j = 0; j < 2 * LW_W; j += 4) {
-        const float4 v = *reinterpret_cast<const float4*>(Sc + lane * (2 * LW_W) + j);
-        sc[j] = v.x; sc[j + 1] = v.y; sc[j + 2] = v.z; sc[j + 3] = v.w;
-      }
-      float m = -INFINITY;
-#pragma unroll
-      for (int j = 0; j < 2 * LW_W; ++j) {
-        const bool ok = j < LW_W ? (w > 0) : (j - LW_W <= lane);
-        sc[j] = ok ? sc[j] : -INFINITY;
-        m = fmaxf(m, sc[j]);
-      }
-      float sum = 0.f;
-#pragma unroll
-      for (int j = 0; j < 2 * LW_W; ++j) {
-        sc[j] = exp2f((sc[j] - m) * 1.4426950408889634f);   // exp2f(-inf) = 0 for the masked keys
-        sum += sc[j];
-      }
-      const float inv = 1.0f / sum;
-#pragma unroll
-      for (int j = 0; j < 2 * LW_W; ++j) P[j * LW_PS + lane] = sc[j] * inv;
-    }
-    __syncwarp();
-    // ---- O = P V, lane = channels (2*lane, 2*lane+1)
-    float2 o[LW_W];
-#pragma unroll
-    for (int q = 0; q < LW_W; ++q) o[q] = make_float2(0.f, 0.f);
-    for (int kk = (w > 0 ? 0 : LW_W); kk < 2 * LW_W; ++kk) {
-      const float2 v = *reinterpret_cast<const float2*>(slab + (kbeg + kk) * LW_ES + 2 * lane);
-      const float4 pa = *reinterpret_cast<const float4*>(P + kk * LW_PS);
-      const float4 pb = *reinterpret_cast<const float4*>(P + kk * LW_PS + 4);
-      const float2 pc = *reinterpret_cast<const float2*>(P + kk * LW_PS + 8);
-      const float pv[LW_W] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w, pc.x, pc.y};
-#pragma unroll
-      for (int q = 0; q < LW_W; ++q) {
-        o[q].x = fmaf(pv[q], v.x, o[q].x);
-        o[q].y = fmaf(pv[q], v.y, o[q].y);
-      }
-    }
-    __syncwarp();                                      // P is rewritten by this warp's next window
-    // ---- second rotation at sequence position t+1 (token 0 is the conditioning token) and the stores
-    const float sg = (lane < 16) ? -1.f : 1.f;         // channels < E/2 take -x[i + E/2], the others +x[i - E/2]
-    const float2* c2p = reinterpret_cast<const float2*>(rcos + (size_t)(t0 + 1) * E + 2 * lane);
-    const float2* s2p = reinterpret_cast<const float2*>(rsin + (size_t)(t0 + 1) * E + 2 * lane);
-    const size_t off0 = ((size_t)seq * S + 1 + t0) * d + head * E + 2 * lane;
-    float* of = x_f32 ? x_f32 + off0 : nullptr;
-    uint16_t* oh = x_h16 ? x_h16 + off0 : nullptr;
-#pragma unroll
-    for (int q = 0; q < LW_W; ++q) {
-      const float px = __shfl_xor_sync(0xffffffffu, o[q].x, 16);
-      const float py = __shfl_xor_sync(0xffffffffu, o[q].y, 16);
-      const float2 c2 = __ldg(c2p + q * (E / 2));
-      const float2 s2 = __ldg(s2p + q * (E / 2));
-      const float y0 = o[q].x * c2.x + sg * px * s2.x;
-      const float y1 = o[q].y * c2.y + sg * py * s2.y;
-      if (of) *reinterpret_cast<float2*>(of + (size_t)q * d) = make_float2(y0, y1);
-      if (oh) *reinterpret_cast<uint32_t*>(oh + (size_t)q * d) = pack_h16x2(y0, y1, h16_fmt);
-    }
-  }
-}
-
-// Tensor-core form of the same fast path (head dim 64, window 10), one warp per window.  The rotated slab is kept as a
+// Fast path for the reference's configuration (head dim 64, window 10) on the tensor cores, one warp per window.  The rotated slab is kept as a
 // 16-bit PAIR (hi = fp16(x), lo = fp16(x - hi): x to ~2^-22 relative), and every product runs as three
 // mma.sync.m16n8k16 passes (hi*hi + hi*lo + lo*hi, fp32 accumulation), so the result keeps fp32-level accuracy while
 // the 10 x 20 x 64 score and 10 x 64 x 20 output products of a window cost 36 + 48 tensor instructions instead of
-// ~1300 FMA instructions (the SIMT kernel above was issue-bound: 87 us for the cfg3 shape against 24 us of HBM time).
+// ~1300 FMA instructions (a SIMT one-warp-per-window kernel, removed, was issue-bound: 87 us for the cfg3 shape against
+// 24 us of HBM time; this one takes 69 us, bound by the legacy HMMA issue rate).
 //   scores  S[16 x 24] = Q[16 x 64] K[24 x 64]^T   (rows 10..15 and keys 20..23 are padding, masked)
 //   softmax on the accumulator fragments (a row lives in the four lanes of a quad)
 //   output  O[16 x 64] = P[16 x 32] V[32 x 64]     (P straight from the score fragments, V through ldmatrix.trans)
@@ -481,44 +352,21 @@ extern "C" int gd_local_attention(const float* z, const float* rope_cos, const f
   const int e = d / heads;
   GD_REQUIRE(e % 2 == 0 && e <= 128, "gd_local_attention: head dim %d must be even and <= 128", e);
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-  const bool fast_ok = e == LW_E && window == LW_W && d % 4 == 0 && al16(z) && al16(rope_cos) && al16(rope_sin) &&
+  const bool fast_ok = e == LM_E && window == LM_W && d % 4 == 0 && al16(z) && al16(rope_cos) && al16(rope_sin) &&
                        (!x_f32 || al16(x_f32)) && (!x_h16 || al16(x_h16));
-  static int use_mma = -1;                                   // GD_LOCAL_MMA=0: the SIMT window kernel
-  if (use_mma < 0) {
-    const char* ev = getenv("GD_LOCAL_MMA");
-    use_mma = ev ? atoi(ev) : 1;
-  }
-  if (fast_ok && use_mma) {
-    const size_t smem_m = (size_t)(T + LM_PAD) * LM_RS * 2 * sizeof(uint16_t);
-    if (smem_m <= 200 * 1024) {
-      static size_t set_m_dev[kMaxDevices] = {};
-      size_t& set_m = set_m_dev[current_device()];
-      if (smem_m > 48 * 1024 && smem_m > set_m) {
-        GD_CUDA_OK(cudaFuncSetAttribute(local_attention_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)smem_m));
-        set_m = smem_m;
-      }
-      local_attention_mma_kernel<<<dim3(heads, n_seq), LM_THREADS, smem_m, (cudaStream_t)stream>>>(
-          z, rope_cos, rope_sin, x_f32, (uint16_t*)x_h16, h16_fmt, T, d, 1.4426950408889634f / sqrtf((float)e));
-      GD_LAUNCH_CHECK();
-      return GD_OK;
+  const size_t smem_m = (size_t)(T + LM_PAD) * LM_RS * 2 * sizeof(uint16_t);
+  if (fast_ok && smem_m <= 200 * 1024) {
+    static size_t set_m_dev[kMaxDevices] = {};
+    size_t& set_m = set_m_dev[current_device()];
+    if (smem_m > 48 * 1024 && smem_m > set_m) {
+      GD_CUDA_OK(cudaFuncSetAttribute(local_attention_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem_m));
+      set_m = smem_m;
     }
-  }
-  if (fast_ok) {
-    const size_t smem_w = ((size_t)T * LW_ES + (LW_THREADS / 32) * (2 * LW_W * LW_PS + LW_W * 2 * LW_W)) * sizeof(float);
-    if (smem_w <= 200 * 1024) {
-      static size_t set_w_dev[kMaxDevices] = {};
-      size_t& set_w = set_w_dev[current_device()];
-      if (smem_w > 48 * 1024 && smem_w > set_w) {
-        GD_CUDA_OK(cudaFuncSetAttribute(local_attention_win_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)smem_w));
-        set_w = smem_w;
-      }
-      local_attention_win_kernel<<<dim3(heads, n_seq), LW_THREADS, smem_w, (cudaStream_t)stream>>>(
-          z, rope_cos, rope_sin, x_f32, (uint16_t*)x_h16, h16_fmt, T, d, 1.0f / sqrtf((float)e));
-      GD_LAUNCH_CHECK();
-      return GD_OK;
-    }
+    local_attention_mma_kernel<<<dim3(heads, n_seq), LM_THREADS, smem_m, (cudaStream_t)stream>>>(
+        z, rope_cos, rope_sin, x_f32, (uint16_t*)x_h16, h16_fmt, T, d, 1.4426950408889634f / sqrtf((float)e));
+    GD_LAUNCH_CHECK();
+    return GD_OK;
   }
   const size_t smem = ((size_t)T * (e + 1) + (LA_THREADS / 32) * e) * sizeof(float);
   GD_REQUIRE(smem <= 200 * 1024, "gd_local_attention: T=%d too long for the shared-memory slab", T);
