@@ -38,7 +38,8 @@ constexpr int kGemmThreads = (2 + kEpiWarps) * 32;
 // MMA issue (tensor pipe ~50 % idle with all operands resident).
 constexpr int kProducerWarp = kEpiWarps, kMmaWarp = kEpiWarps + 1;
 
-enum { EPI_GENERIC = 0, EPI_BIAS_H16 = 1, EPI_BIAS_GELU_H16 = 2, EPI_BIAS_RES_F32 = 3, EPI_QUAD = 4, EPI_OUT_T = 5 };
+enum { EPI_GENERIC = 0, EPI_BIAS_H16 = 1, EPI_BIAS_GELU_H16 = 2, EPI_BIAS_RES_F32 = 3, EPI_QUAD = 4, EPI_OUT_T = 5,
+       EPI_QUAD_IN1 = 6, EPI_QUAD_IN2 = 7 };
 
 // One CTA per 128 x BN tile.  (A cta_group::2 variant -- CTA pair per 256 x BN tile, W tile split between the pair --
 // was built and parity-tested in round 1 and measured slower at every encoder shape, 42.1 vs 39.9 us for QKV; it was
@@ -236,7 +237,20 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           ptx::tmem_ld_32x32(taddr0 + c, v);
           if (m_warp + lane < M) epilogue_row_chunk<32>(ep, m_warp + lane, n0, N, v);
         }
-      } else if constexpr (EPI == EPI_QUAD) {
+      } else if constexpr (EPI == EPI_QUAD || EPI == EPI_QUAD_IN1 || EPI == EPI_QUAD_IN2) {
+        // EPI_QUAD_IN1 / _IN2 are the same code with the feature tests of the two input projections folded at compile
+        // time (the generic form runs ~3 k instructions per warp and tile, most of them tests and address arithmetic:
+        // it was issue-bound at 3x the main loop's time):
+        //   IN1 (V1: poseEmbedding + pe)   bias, row table, row map, 2 copies, fp32 + 16-bit out
+        //   IN2 (V2: project_to_lat)       row table, per-sequence bias, 2 copies, fp32 out
+        constexpr bool kSpec = EPI != EPI_QUAD;
+        const bool has_bias = kSpec ? (EPI == EPI_QUAD_IN1) : ep.bias != nullptr;
+        const bool has_tab = kSpec ? true : ep.rowtab != nullptr;
+        const bool has_seq = kSpec ? (EPI == EPI_QUAD_IN2) : ep.seqbias != nullptr;
+        const bool has_res = kSpec ? false : ep.residual != nullptr;
+        const bool has_f32 = kSpec ? true : ep.out_f32 != nullptr;
+        const bool has_h16 = kSpec ? (EPI == EPI_QUAD_IN1) : ep.out_h16 != nullptr;
+        const bool has_map = kSpec ? (EPI == EPI_QUAD_IN1) : ep.map_t > 0;
         // Every linear gdEpilogue feature (bias, row table, per-sequence bias, residual, row map, copies; no
         // activation, no out_t) on row-contiguous quads: TMEM -> registers (row = lane) -> this warp's swizzled
         // staging block -> lane (it, c4) takes columns 4*c4 .. 4*c4+3 of row 4*it + lane/8, so table, residual and
@@ -245,9 +259,9 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
         int tabrow[8], outrow[8], seqrow[8];                 // of this lane's eight quad rows (4*it + lane/8)
         {
           const int mm = m_warp + lane;                      // computed for row `lane`, handed over by shuffle
-          const int tabrow_l = ep.rowtab ? (mm % ep.tab_period) + ep.tab_offset : 0;
-          const int seqrow_l = ep.seqbias ? mm / ep.seq_rows : 0;
-          const int mapped = ep.map_t > 0 ? (mm / ep.map_t) * ep.map_s + ep.map_off + (mm % ep.map_t) : mm;
+          const int tabrow_l = has_tab ? (mm % ep.tab_period) + ep.tab_offset : 0;
+          const int seqrow_l = has_seq ? mm / ep.seq_rows : 0;
+          const int mapped = has_map ? (mm / ep.map_t) * ep.map_s + ep.map_off + (mm % ep.map_t) : mm;
           const int outrow_l = mm < M ? mapped : -1;
 #pragma unroll
           for (int it = 0; it < 8; ++it) {
@@ -257,7 +271,7 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
             outrow[it] = __shfl_sync(0xffffffffu, outrow_l, rl);
           }
         }
-        const int ncopy = ep.dup > 1 ? ep.dup : 1;
+        const int ncopy = kSpec ? 2 : (ep.dup > 1 ? ep.dup : 1);
         // bias + the row-table quads of a chunk (HBM latency when the table is per row, as in the V2 input
         // projection): eight independent loads issued together, ahead of the TMEM load.  (Fetching them a whole
         // chunk ahead measured slower: 62 vs 54 us on the V2 shape -- the epilogue is issue-bound, not latency-bound.)
@@ -265,25 +279,40 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           const int n = n_base + c + c4 * 4;
           const bool col_ok = n < N;                         // N % 4 == 0: a quad is inside or outside
           float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (ep.bias && col_ok) bias4 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
+          if (has_bias && col_ok) bias4 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
 #pragma unroll
           for (int it = 0; it < 8; ++it) {
             pre[it] = bias4;
-            if (ep.rowtab && col_ok && outrow[it] >= 0)
+            if (has_tab && col_ok && outrow[it] >= 0)
               f4_add(pre[it], __ldg(reinterpret_cast<const float4*>(ep.rowtab + (size_t)tabrow[it] * ep.ld_tab + n)));
           }
         };
-        float4 pre[8];
+        // The specialised forms with two chunks per warp (BN = 128) request the table quads of BOTH chunks before they
+        // wait for the accumulator: the V2 table is per row and comes from HBM, and with the lean code the epilogue is no
+        // longer issue-bound (the generic form measured slower with a chunk of look-ahead).
+        constexpr bool kAhead = kSpec && kColsPerWarp == 64;
+        float4 pre[8], pre_b[8];
+        if constexpr (kAhead) {
+          prefetch(0, pre);
+          prefetch(32, pre_b);
+        }
         ptx::mbar_wait(&tfull_bar[buf], use & 1);
         ptx::tc_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
-#pragma unroll 1
+#pragma unroll(kAhead ? 2 : 1)
         for (int c = 0; c < kColsPerWarp; c += 32) {
           const int n0 = n_base + c;
           if (n0 >= N) break;                                // warp-uniform
           uint32_t v[32];
           ptx::tmem_ld_32x32_nowait(taddr0 + c, v);
-          prefetch(c, pre);                                  // in flight during the TMEM load and the staging
+          if constexpr (kAhead) {
+            if (c == 32) {
+#pragma unroll
+              for (int it = 0; it < 8; ++it) pre[it] = pre_b[it];
+            }
+          } else {
+            prefetch(c, pre);                                // in flight during the TMEM load and the staging
+          }
           const int n = n0 + c4 * 4;
           const bool col_ok = n < N;
           ptx::tmem_ld_wait_on(v);
@@ -296,16 +325,17 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
             w[it] = ptx::lds_v4(stg + rl * 128 + ((c4 ^ (rl & 7)) << 4));
             f4_add(w[it], pre[it]);
           }
+#pragma unroll 2
           for (int cp = 0; cp < ncopy; ++cp) {
             float4 o[8];
 #pragma unroll
             for (int it = 0; it < 8; ++it) {                 // all loads of the copy before any store
               o[it] = w[it];
               if (outrow[it] < 0 || !col_ok) continue;
-              if (ep.seqbias)
+              if (has_seq)
                 f4_add(o[it], __ldg(reinterpret_cast<const float4*>(
                                   ep.seqbias + (size_t)(cp * ep.seq_count + seqrow[it]) * ep.ld_seq + n)));
-              if (ep.residual)
+              if (has_res)
                 f4_add(o[it], *reinterpret_cast<const float4*>(
                                   ep.residual + ((size_t)outrow[it] + (size_t)cp * ep.dup_row_stride) * ep.ld_res + n));
             }
@@ -313,8 +343,8 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
             for (int it = 0; it < 8; ++it) {
               if (outrow[it] < 0 || !col_ok) continue;
               const size_t r = (size_t)outrow[it] + (size_t)cp * ep.dup_row_stride;
-              if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + r * ep.ld_out + n) = o[it];
-              if (ep.out_h16) {
+              if (has_f32) *reinterpret_cast<float4*>(ep.out_f32 + r * ep.ld_out + n) = o[it];
+              if (has_h16) {
                 uint2 pk;
                 pk.x = pack_h16x2(o[it].x, o[it].y, ep.h16_fmt);
                 pk.y = pack_h16x2(o[it].z, o[it].w, ep.h16_fmt);
@@ -562,7 +592,11 @@ static int pick_epilogue(const gdEpilogue* ep, int N) {
                        (!ep->residual || (al16(ep->residual) && ep->ld_res % 4 == 0)) &&
                        (!ep->out_f32 || (al16(ep->out_f32) && ep->ld_out % 4 == 0)) &&
                        (!ep->out_h16 || (al16(ep->out_h16) && ep->ld_out_h16 % 4 == 0));
-  const int fallback = quad_ok ? EPI_QUAD : EPI_GENERIC;
+  int fallback = quad_ok ? EPI_QUAD : EPI_GENERIC;
+  if (quad_ok && ep->dup == 2 && ep->rowtab && !ep->residual && ep->out_f32) {       // the two input projections
+    if (ep->bias && !ep->seqbias && ep->map_t > 0 && ep->out_h16) fallback = EPI_QUAD_IN1;
+    if (!ep->bias && ep->seqbias && ep->map_t <= 0 && !ep->out_h16) fallback = EPI_QUAD_IN2;
+  }
   if (N % 32 != 0 || !ep->bias || !al16(ep->bias) || ep->rowtab || ep->seqbias || ep->map_t > 0 || ep->dup > 1)
     return fallback;
   if (ep->out_h16 && !ep->out_f32 && !ep->residual && al16(ep->out_h16) && ep->ld_out_h16 % 8 == 0) {
@@ -656,6 +690,8 @@ extern "C" int gd_gemm_h16(const void* A, int32_t lda, const void* W, int32_t ld
     GD_GEMM_CASE(EPI_BIAS_GELU_H16)
     GD_GEMM_CASE(EPI_BIAS_RES_F32)
     GD_GEMM_CASE(EPI_QUAD)
+    GD_GEMM_CASE(EPI_QUAD_IN1)
+    GD_GEMM_CASE(EPI_QUAD_IN2)
     GD_GEMM_CASE(EPI_OUT_T)
     default: break;
   }
