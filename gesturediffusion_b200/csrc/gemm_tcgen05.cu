@@ -361,6 +361,14 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
         const int seq = mm / ep.t_s, s_in = mm - seq * ep.t_s;
         const bool row_ok = mm < M && s_in >= ep.t_skip;
         float* orow = ep.out_t + (size_t)seq * N * ep.t_t + (s_in - ep.t_skip);
+        // the first chunk's bias (32 warp-uniform loads) is requested before the accumulator wait, the next chunk's while
+        // this chunk's stores drain: fetched inside the store loop they were 32 dependent L1 round trips per chunk
+        float bv[32];
+        auto load_bias = [&](int n0) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) bv[i] = (ep.bias && n0 + i < N) ? __ldg(ep.bias + n0 + i) : 0.f;
+        };
+        if (n_base < N) load_bias(n_base);
         ptx::mbar_wait(&tfull_bar[buf], use & 1);
         ptx::tc_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN + half * kColsPerWarp);
@@ -371,11 +379,14 @@ gemm_h16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
           uint32_t v[32];
           ptx::tmem_ld_32x32_nowait(taddr0 + c, v);
           ptx::tmem_ld_wait_on(v);
+          float o[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(v[i]) + bv[i];
+          if (c + 32 < kColsPerWarp && n0 + 32 < N) load_bias(n0 + 32);
           if (row_ok) {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-              if (n0 + i < N)
-                orow[(size_t)(n0 + i) * ep.t_t] = __uint_as_float(v[i]) + (ep.bias ? __ldg(ep.bias + n0 + i) : 0.f);
+              if (n0 + i < N) orow[(size_t)(n0 + i) * ep.t_t] = o[i];
           }
         }
       } else if constexpr (EPI == EPI_BIAS_H16 || EPI == EPI_BIAS_GELU_H16) {
