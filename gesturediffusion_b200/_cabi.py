@@ -17,7 +17,7 @@ EXPORTED_SYMBOLS = [
     "gd_abi_version", "gd_last_error", "gd_gemm_h16", "gd_gemm_f32", "gd_gemm_h16_ln", "gd_gemm_h16_ln_split", "gd_ffn_h16_ln_split", "gd_ffn_trace", "gd_attention_h16",
     "gd_attention_f32", "gd_layernorm", "gd_local_attention", "gd_cond_tokens", "gd_posterior_step",
     "gd_pack_rows", "gd_unnormalize_split", "gd_q_sample", "gd_philox_normal", "gd_set_loop_state", "gd_launch_count",
-    "gd_noalloc_max_elems", "gd_linear_res_ln_f32_noalloc",
+    "gd_noalloc_max_elems", "gd_linear_res_ln_f32_noalloc", "gd_gemm_ln_small_max_rows",
 ]
 
 _p, _i32, _i64, _u64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_float
@@ -88,6 +88,7 @@ def load():
         "gd_attention_f32": [_p, _p, _i32, _i32, _i32, _i32, _p],
         "gd_layernorm": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _f32, _p],
         "gd_noalloc_max_elems": [],
+        "gd_gemm_ln_small_max_rows": [],
         "gd_linear_res_ln_f32_noalloc": [_p, _i32, _p, _i32, _i32, _i32, _i32, _p, _p, _i32, _p, _p, _f32, _p, _p, _i32,
                                          _p],
         "gd_local_attention": [_p, _p, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p],

@@ -579,6 +579,7 @@ namespace gd {
 int launch_gemm_ln_small(const void* A, int lda, const void* W, int ldw, int M, int K, int fmt, const float* bias,
                          const float* residual, int ld_res, const float* gamma, const float* beta, float eps,
                          float* out_f32, int ld_out, void* out_h16, int ld_out_h16, int h16_fmt, cudaStream_t stream);
+int gemm_ln_small_max_rows();
 }
 
 extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
@@ -603,13 +604,8 @@ extern "C" int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t
                  (!out_h16 || (ld_out_h16 >= N && ld_out_h16 % 8 == 0)),
              "gd_gemm_h16_ln: leading dimensions must be >= N and multiples of 4 (16-bit output: 8)");
   {
-    // few rows: an 8-CTA cluster per row tile (gemm_ln_small.cu).  GD_LN_SMALL_MAX_ROWS moves the crossover (0 = never).
-    static int small_rows = -1;
-    if (small_rows < 0) {
-      const char* e = getenv("GD_LN_SMALL_MAX_ROWS");
-      small_rows = e ? atoi(e) : 2304;
-    }
-    if (N == 512 && M <= small_rows)
+    // few rows: an 8-CTA cluster per row tile (gemm_ln_small.cu), while all row tiles fit the GPU at once
+    if (N == 512 && M <= gemm_ln_small_max_rows())
       return launch_gemm_ln_small(A, lda, W, ldw, M, K, fmt, bias, residual, ld_res, gamma, beta, eps, out_f32, ld_out,
                                   out_h16, ld_out_h16, h16_fmt, (cudaStream_t)stream);
   }

@@ -119,8 +119,11 @@ class DenoiserEngine:
         # B = 1: 0.346 / 0.293, 8: 0.387 / 0.333, 16: 0.453 / 0.403, 24 (4728 rows): 0.497 / 0.445, 32 (6304 rows):
         # 0.541 / 0.594, 64: 0.862 / 0.960.
         self.fuse_ln_min_rows = int(os.environ.get("GD_FUSE_LN_MIN_ROWS", "5500"))
-        # ... and up to this many rows the library's few-row form of the same call (one 8-CTA cluster per row tile)
-        self.fuse_ln_small_max_rows = int(os.environ.get("GD_LN_SMALL_MAX_ROWS", "2304"))
+        # ... and up to this many rows the library's few-row form of the same call (one 8-CTA cluster per row tile): the
+        # library says how many rows fit this GPU in one wave of clusters (gd_gemm_ln_small_max_rows; GD_LN_SMALL_MAX_ROWS
+        # overrides it there)
+        with torch.cuda.device(device):
+            self.fuse_ln_small_max_rows = int(K._cabi.load().gd_gemm_ln_small_max_rows())
         self._pack(state_dict)
 
     # ------------------------------------------------------------------ weights

@@ -90,6 +90,11 @@ int gd_gemm_f32(const float* A, int32_t lda, const float* W, int32_t ldw,
  * shared memory); other widths return GD_ERR_UNSUPPORTED and callers use gd_gemm_h16 + gd_layernorm.
  * residual may alias out_f32 (each element is read before it is written, by the same warp).  ld_res / ld_out are
  * multiples of 4 elements, ld_out_h16 of 8 (the outputs leave through TMA stores). */
+/* Largest M for which gd_gemm_h16_ln (N = 512) runs its few-row form -- one 8-CTA cluster per 128-row tile, all tiles
+ * resident at once: 128 x the number of such clusters the current device holds (cudaOccupancyMaxActiveClusters), at most
+ * 2304; environment GD_LN_SMALL_MAX_ROWS overrides (0 = never).  Callers that choose between this call and
+ * gd_gemm_h16 + gd_layernorm for small batches (the engine) ask here.  No reference counterpart (dispatch helper). */
+int gd_gemm_ln_small_max_rows(void);
 int gd_gemm_h16_ln(const void* A, int32_t lda, const void* W, int32_t ldw, int32_t M, int32_t N, int32_t K,
                    int32_t fmt, const float* bias, const float* residual, int32_t ld_res,
                    const float* gamma, const float* beta, float eps, float* out_f32, int32_t ld_out,
