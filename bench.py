@@ -440,7 +440,8 @@ def dominant_kernel_roofline(c, peaks, profile_out):
                 "traffic_over_algorithmic": (traffic / by0) if traffic else None,
                 "l2_to_sm_over_algorithmic": (l2_to_sm / by0) if l2_to_sm else None,
                 "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
-                "launch_ms": t0 / c0, "share_of_step": t0 / tot, "algorithmic_bytes_per_launch": by0,
+                "launch_ms": t0 / c0, "share_of_step": t0 / tot, "_launches_per_step": c0 / 6.0,
+                "algorithmic_bytes_per_launch": by0,
                 "algorithmic_flops_per_launch": fl0,
                 "tensor_tflops_same_kernel": fl0 / sec / 1e12,
                 "all_gemms": {"achieved": fl_all / (tt * 1e-3) / 1e12, "unit": "TFLOP/s",
@@ -549,6 +550,18 @@ def run_b200(args):
     if rank != 0:
         return
     step_tflops = flops_step / (ms_step / D * 1e-3) / 1e12
+    if roof is not None:
+        # The eager pass that carries the per-launch events cannot overlap a kernel's prologue with its predecessor (no
+        # programmatic dependent launch across an event record), so `launch_ms` is a few us above what the kernel costs
+        # inside the step graph.  Extra, clearly labelled estimate: the kernel's share of the eager pass x the graph's
+        # time per denoise step / its launches per step (`frac` itself stays the directly measured figure).
+        per_step = roof.pop("_launches_per_step", None)
+        if per_step:
+            est_ms = roof["share_of_step"] * (ms_step / D) / per_step
+            scale = roof["launch_ms"] / est_ms
+            roof["in_graph_estimate"] = {"launch_ms": est_ms, "achieved": roof["achieved"] * scale,
+                                         "frac": roof["frac"] * scale,
+                                         "how": "share_of_step x graph ms per denoise step / launches per step"}
     line = {"metric": "motion frames/sec (CFG DDPM sampling)", "value": value, "unit": "frames/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "ms_per_denoise_step": ms_step / D, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
